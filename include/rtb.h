@@ -1,0 +1,190 @@
+/* rtb.h -- C ABI of the B200-native hot path of the glTF path tracer (librtb.so).
+ *
+ * The reference (Korinin38/raytracing-hw) has no plugin / FFI surface: it is one process,
+ * `run.sh input.gltf width height samples [output.ppm]` (run.sh:2, src/main.cpp:22-58).  The seam this
+ * library replaces is the pair of const member functions the reference's main() reaches after the Scene
+ * constructor has built the BVH and the light distribution:
+ *
+ *     BVH::intersect(const std::vector<Primitive>&, Ray)      src/core/bvh.h:24,  src/core/bvh.cpp:239-243
+ *     Scene::render(ProgressFunc)                             src/core/scene.h:19, src/core/scene.cpp:17-65
+ *
+ * Everything is `extern "C"`, plain pointers and sizes, int status codes (0 = ok); the message of the last
+ * failure on the calling thread is returned by rtb_last_error().  No exception crosses this boundary; the C++
+ * host (raytracing-hw_b200/host/main.cpp) re-throws std::runtime_error to keep the reference's
+ * abort-on-error behaviour.  There is NO CPU fallback: every compute entry point fails with RTB_ERR_NO_DEVICE
+ * when no CUDA device is usable.
+ *
+ * Threading: a scene may be used from one host thread at a time.  Device selection is per scene.
+ */
+#ifndef RTB_H_
+#define RTB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTB_OK 0
+#define RTB_ERR_INVALID 1      /* bad argument / malformed scene description            */
+#define RTB_ERR_NO_DEVICE 2    /* no usable CUDA device (never falls back to the CPU)    */
+#define RTB_ERR_CUDA 3         /* a CUDA runtime call or kernel failed                   */
+#define RTB_ERR_IO 4           /* file could not be read / written / parsed              */
+
+/* Closest-hit culling policy (see DESIGN.md "culling modes").
+ *  REFERENCE: visits exactly the nodes BVH::intersectHelper visits (src/core/bvh.cpp:177-237): the near child is
+ *             always entered, only the far sibling is culled, against the best hit of the near sibling's subtree.
+ *             Bit-exact ids by construction.
+ *  GLOBAL   : same visit order, but every box is culled against the best hit found so far.  Visits a subset; ids are
+ *             identical unless a triangle's t rounds below the entry distance of a box that contains it while another
+ *             hit lies between the two values (documented tie case).                                                */
+#define RTB_CULL_REFERENCE 0
+#define RTB_CULL_GLOBAL 1
+
+typedef struct rtb_scene rtb_scene;            /* device-resident scene (one GPU)            */
+typedef struct rtb_host_scene rtb_host_scene;  /* host-side scene: glTF load + BVH build     */
+
+typedef struct rtb_texture_desc {
+    int32_t width, height;
+    const uint8_t *rgba;        /* width*height*4 bytes, row-major, as tinygltf/stb_image deliver (always 4 channels) */
+} rtb_texture_desc;
+
+/* Flat scene description, all arrays borrowed for the duration of rtb_scene_create only.
+ * Mirrors what Scene holds after its constructor (src/core/scene.cpp:197-249):                                     */
+typedef struct rtb_scene_desc {
+    /* scene BVH in REFERENCE node order (struct Node, src/core/bvh.h:10-17) */
+    uint32_t n_nodes;
+    const float *node_aabb;       /* n_nodes x 6 : min xyz, max xyz                                                  */
+    const int32_t *node_links;    /* n_nodes x 5 : left, right, split_dim, first_primitive_id, primitive_count; -1 = invalidKey */
+    /* triangles in POST-BUILD order (BVH::buildBVH reorders Scene::objects, src/core/bvh.cpp:166) */
+    uint32_t n_tris;
+    const float *tri_pos;         /* n x 9  : p0, U = p1-p0, V = p2-p0   (Primitive::position, src/geometry/primitive.h:101) */
+    const float *tri_nrm;         /* n x 9  : per-vertex normals          (Primitive::normal)                          */
+    const float *tri_tan;         /* n x 12 : per-vertex tangents xyzw    (Primitive::tangent)                         */
+    const float *tri_uv;          /* n x 6  : per-vertex texcoords        (Primitive::texcoord)                        */
+    const int32_t *tri_mesh;      /* n      : Primitive::mesh_id                                                       */
+    /* meshes (struct Mesh / Material, src/geometry/primitive.h:76-94) */
+    uint32_t n_meshes;
+    const float *mesh_material;   /* n x 16 : ior, alpha, base rgb, emission rgb, metallic, roughness2,
+                                              base_color_i, normal_i, metallic_roughness_i, emission_i (as float, -1 = none), 0, 0 */
+    const double *mesh_normal_transform; /* n x 16, column-major matrix4d                                              */
+    uint32_t n_textures;
+    const rtb_texture_desc *textures;
+    /* light list: emissive triangles re-ordered by their own BVH (rng::ManyLightsDistribution, src/utils/random.cpp:156-167) */
+    uint32_t n_lights;
+    const float *light_pos;       /* n_lights x 9 : p0, U, V                                                          */
+    uint32_t n_light_nodes;
+    const float *light_node_aabb; /* n_light_nodes x 6                                                                */
+    const int32_t *light_node_links; /* n_light_nodes x 5                                                             */
+    /* camera (class Camera, src/core/camera.h:13-45) */
+    float cam_pos[3];
+    float cam_axes[9];            /* right, up, forward                                                               */
+    float cam_tan_half_fov[2];    /* tanf(fov_x/2), tanf(fov_y/2) evaluated by the HOST libm (camera.cpp:51-52)       */
+    /* integrator constants */
+    int32_t ray_depth;            /* 6  (src/io/scene_parser.cpp:17)                                                  */
+    float max_distance;           /* zfar or 1e9 (src/io/scene_parser.cpp:22,119-120)                                 */
+    float bg_color[3];            /* 0,0,0 (src/core/scene.cpp:203)                                                   */
+} rtb_scene_desc;
+
+typedef struct rtb_render_params {
+    int32_t width, height;        /* canvas size (CLI arguments 2 and 3)                                              */
+    int32_t samples;              /* samples per pixel (CLI argument 4)                                               */
+    int32_t row_begin, row_end;   /* rows [row_begin,row_end) rendered by this call (tile split); 0,height = all     */
+    uint32_t pixel0_seed;         /* engine seed of pixel 0 (the reference uses std::random_device there,
+                                     src/utils/random.cpp:12-18); 0 is mapped to 1 as minstd_rand::seed does          */
+    int32_t sample_begin;         /* reserved, must be 0: all samples of a pixel share ONE sequential engine stream
+                                     (src/core/scene.cpp:34-35), so a pixel's sample range cannot be cut              */
+    int32_t flags;                /* RTB_RENDER_* bits                                                                */
+    /* multi-GPU tile split: rows [row_begin,row_end) are cut into blocks of `interleave_rows` rows (a multiple of 4);
+     * this call renders the blocks b with b % interleave_count == interleave_index and writes them COMPACTLY, in block
+     * order, into accum / rgb8 (rtb_render_local_rows() rows).  interleave_count <= 1: every row, as one range.        */
+    int32_t interleave_count, interleave_index, interleave_rows;
+} rtb_render_params;
+
+/* number of rows a call with these parameters renders (and its output buffers hold); -1 on invalid parameters */
+int rtb_render_local_rows(const rtb_render_params *params);
+/* global row of local row `local_row` of such a call */
+int rtb_render_global_row(const rtb_render_params *params, int local_row);
+
+#define RTB_RENDER_COUNTERS 1        /* also count box / triangle tests (slower instantiation of the kernel); rays and
+                                        light queries are always counted                                                */
+#define RTB_RENDER_REFERENCE_CULL 2  /* traverse with RTB_CULL_REFERENCE instead of the default RTB_CULL_GLOBAL          */
+
+/* set rtb_stats.box_tests to this value before a call to ask for box/triangle test counts (a slower, counting
+ * instantiation of the kernel is launched); otherwise box_tests / tri_tests come back 0.                          */
+#define RTB_REQUEST_COUNTERS 0xFFFFFFFFFFFFFFFFull
+
+typedef struct rtb_stats {
+    uint64_t closest_hit_rays;    /* Scene::intersect entries with power > 0 (primary + secondary)                    */
+    uint64_t light_pdf_queries;   /* BVH::intersectAll queries (src/utils/random.cpp:183)                             */
+    uint64_t box_tests;           /* ray/AABB tests (closest-hit + light queries), 0 unless requested (see above)     */
+    uint64_t tri_tests;           /* ray/triangle tests,                           0 unless requested                 */
+    double kernel_ms;             /* device time of the render / closest-hit kernels of this call (CUDA events)       */
+    double h2d_ms, d2h_ms;        /* copies inside this call                                                          */
+    uint64_t launches;            /* kernels launched by this call                                                    */
+} rtb_stats;
+
+const char *rtb_last_error(void);
+int rtb_device_count(void);
+
+/* ------------------------------------------------------------------------------------------------ host side
+ * glTF loading and BVH construction stay on the C++ host (north_star); these produce a flat rtb_scene_desc whose
+ * node and triangle layout equals the reference's (verified node-for-node in tests/test_layout.py).               */
+
+/* parse_scene_gltf + Scene::Scene (src/io/scene_parser.cpp:25-350, src/core/scene.cpp:197-249) */
+int rtb_host_scene_load_gltf(const char *path, int width, int height, int samples, rtb_host_scene **out);
+/* a triangle soup given as 3 world-space vertices per triangle (n x 9 floats); normals may be NULL (flat);
+ * triangles [emissive_from, n) are emissive (1,1,1).  Camera as in rtb_scene_desc.                               */
+int rtb_host_scene_from_triangles(const float *verts9, const float *nrm9, size_t n, size_t emissive_from,
+                                  const float cam_pos[3], const float cam_axes[9], float fov_x, float fov_y,
+                                  float max_distance, rtb_host_scene **out);
+/* fills *desc with pointers into the host scene (valid until rtb_host_scene_destroy) */
+int rtb_host_scene_desc(const rtb_host_scene *hs, rtb_scene_desc *desc);
+/* BVH statistics the reference prints (src/core/scene.cpp:233-246): counts[0..4] = nodes with 0..4 primitives */
+int rtb_host_scene_bvh_stats(const rtb_host_scene *hs, uint64_t *n_nodes, uint64_t counts5[5], uint64_t *max_leaf);
+double rtb_host_scene_build_seconds(const rtb_host_scene *hs);
+void rtb_host_scene_destroy(rtb_host_scene *hs);
+
+/* ------------------------------------------------------------------------------------------------ device side */
+
+/* Uploads the scene to CUDA device `device` (converts nodes to the 64-byte two-child layout). */
+int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out);
+void rtb_scene_destroy(rtb_scene *scene);
+int rtb_scene_device(const rtb_scene *scene);
+/* bytes of device memory holding nodes+triangles (the traversal working set) */
+size_t rtb_scene_traversal_bytes(const rtb_scene *scene);
+
+/* Replaces BVH::intersect (src/core/bvh.cpp:239-243) for a batch.  rays6: n x 6 floats = origin xyz, direction xyz
+ * (un-normalised; normalised on device exactly as Ray::Ray does, src/geometry/primitive.cpp:12-15).
+ * Outputs (any may be NULL except id): id = index into the post-build triangle array, -1 on a miss; t,u,v as
+ * Intersection::distance/local_coords; inside as Intersection::inside.  HOST pointers; copies are inside the call. */
+int rtb_closest_hit(rtb_scene *scene, const float *rays6, size_t n, int cull_mode,
+                    int32_t *id, float *t, float *u, float *v, uint8_t *inside, rtb_stats *stats);
+/* same, DEVICE pointers (caller-owned, e.g. torch tensors), launched on `stream` (a cudaStream_t, may be 0);
+ * asynchronous; counters (may be NULL) = device pointer to 2 uint64 {box tests, triangle tests}.                  */
+int rtb_closest_hit_device(rtb_scene *scene, const float *d_rays6, size_t n, int cull_mode,
+                           int32_t *d_id, float *d_t, float *d_u, float *d_v, uint8_t *d_inside,
+                           unsigned long long *d_counters, void *stream);
+
+/* Replaces ManyLightsDistribution::pdf (src/utils/random.cpp:179-188) for a batch (test/diagnostic entry). */
+int rtb_light_pdf(rtb_scene *scene, const float *rays6, size_t n, float *pdf);
+
+/* Replaces Scene::render (src/core/scene.cpp:17-65).  Renders rows [row_begin,row_end) at `samples` spp.
+ * accum (may be NULL): (row_end-row_begin) x width x 3 floats, the per-pixel radiance SUMS before the resolve;
+ * rgb8  (may be NULL): (row_end-row_begin) x width x 3 bytes after x(1/samples), ACES, gamma 1/2.2, round.
+ * HOST pointers; the device->host copy is inside the call.                                                         */
+int rtb_render(rtb_scene *scene, const rtb_render_params *params, float *accum, uint8_t *rgb8, rtb_stats *stats);
+/* same, DEVICE output pointers, asynchronous on `stream`; d_counters: 4 uint64 {rays, light queries, box, tri} or NULL */
+int rtb_render_device(rtb_scene *scene, const rtb_render_params *params, float *d_accum, uint8_t *d_rgb8,
+                      unsigned long long *d_counters, void *stream);
+/* resolve only (src/core/scene.cpp:54-63): d_accum (n_pixels x 3 sums) -> d_rgb8 */
+int rtb_resolve_device(const float *d_accum, size_t n_pixels, int samples, uint8_t *d_rgb8, void *stream);
+
+/* Canvas::write_to (src/render/canvas.h:76-89): "P6\n<W> <H>\n255\n" + W*H*3 bytes */
+int rtb_write_ppm(const char *path, int width, int height, const uint8_t *rgb8);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTB_H_ */

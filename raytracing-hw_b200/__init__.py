@@ -1,0 +1,293 @@
+"""ctypes binding of librtb.so (include/rtb.h) -- host plumbing for the tests and bench.py.
+
+The product is the C ABI + the sm_100a kernels behind it; this module only loads the shared library, builds the
+argument structs and hands over numpy / torch buffers.  It never computes anything itself and has NO fallback:
+if librtb.so is missing or no CUDA device is usable, the calls raise.
+
+Import (the directory name contains a hyphen):  rtb = importlib.import_module("raytracing-hw_b200")
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librtb.so")
+
+RTB_OK, RTB_ERR_INVALID, RTB_ERR_NO_DEVICE, RTB_ERR_CUDA, RTB_ERR_IO = 0, 1, 2, 3, 4
+CULL_REFERENCE, CULL_GLOBAL = 0, 1
+REQUEST_COUNTERS = 0xFFFFFFFFFFFFFFFF
+
+# every symbol include/rtb.h declares (tests/test_abi.py checks the library exports all of them)
+ABI_SYMBOLS = [
+    "rtb_last_error", "rtb_device_count",
+    "rtb_host_scene_load_gltf", "rtb_host_scene_from_triangles", "rtb_host_scene_desc", "rtb_host_scene_bvh_stats",
+    "rtb_host_scene_build_seconds", "rtb_host_scene_destroy",
+    "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_device", "rtb_scene_traversal_bytes",
+    "rtb_closest_hit", "rtb_closest_hit_device", "rtb_light_pdf",
+    "rtb_render", "rtb_render_device", "rtb_resolve_device", "rtb_render_local_rows", "rtb_render_global_row",
+    "rtb_write_ppm",
+]
+
+
+class TextureDesc(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("rgba", C.c_void_p)]
+
+
+class SceneDesc(C.Structure):
+    _fields_ = [
+        ("n_nodes", C.c_uint32), ("node_aabb", C.c_void_p), ("node_links", C.c_void_p),
+        ("n_tris", C.c_uint32), ("tri_pos", C.c_void_p), ("tri_nrm", C.c_void_p), ("tri_tan", C.c_void_p),
+        ("tri_uv", C.c_void_p), ("tri_mesh", C.c_void_p),
+        ("n_meshes", C.c_uint32), ("mesh_material", C.c_void_p), ("mesh_normal_transform", C.c_void_p),
+        ("n_textures", C.c_uint32), ("textures", C.POINTER(TextureDesc)),
+        ("n_lights", C.c_uint32), ("light_pos", C.c_void_p),
+        ("n_light_nodes", C.c_uint32), ("light_node_aabb", C.c_void_p), ("light_node_links", C.c_void_p),
+        ("cam_pos", C.c_float * 3), ("cam_axes", C.c_float * 9), ("cam_tan_half_fov", C.c_float * 2),
+        ("ray_depth", C.c_int32), ("max_distance", C.c_float), ("bg_color", C.c_float * 3),
+    ]
+
+
+class RenderParams(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("samples", C.c_int32), ("row_begin", C.c_int32),
+                ("row_end", C.c_int32), ("pixel0_seed", C.c_uint32), ("sample_begin", C.c_int32), ("flags", C.c_int32),
+                ("interleave_count", C.c_int32), ("interleave_index", C.c_int32), ("interleave_rows", C.c_int32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("closest_hit_rays", C.c_uint64), ("light_pdf_queries", C.c_uint64), ("box_tests", C.c_uint64),
+                ("tri_tests", C.c_uint64), ("kernel_ms", C.c_double), ("h2d_ms", C.c_double), ("d2h_ms", C.c_double),
+                ("launches", C.c_uint64)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class RtbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("librtb error %d: %s" % (code, msg))
+        self.code = code
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("%s is missing: run `python -c 'import __graft_entry__ as g; g.build()'` or ./build.sh "
+                               "(there is no fallback path)" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        L.rtb_last_error.restype = C.c_char_p
+        L.rtb_host_scene_build_seconds.restype = C.c_double
+        L.rtb_host_scene_build_seconds.argtypes = [C.c_void_p]
+        L.rtb_scene_traversal_bytes.restype = C.c_size_t
+        L.rtb_scene_traversal_bytes.argtypes = [C.c_void_p]
+        L.rtb_host_scene_load_gltf.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.rtb_host_scene_from_triangles.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p, C.c_void_p,
+                                                    C.c_float, C.c_float, C.c_float, C.POINTER(C.c_void_p)]
+        L.rtb_host_scene_desc.argtypes = [C.c_void_p, C.POINTER(SceneDesc)]
+        L.rtb_host_scene_bvh_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64 * 5), C.POINTER(C.c_uint64)]
+        L.rtb_host_scene_destroy.argtypes = [C.c_void_p]
+        L.rtb_host_scene_destroy.restype = None
+        L.rtb_scene_create.argtypes = [C.POINTER(SceneDesc), C.c_int, C.POINTER(C.c_void_p)]
+        L.rtb_scene_destroy.argtypes = [C.c_void_p]
+        L.rtb_scene_destroy.restype = None
+        L.rtb_scene_device.argtypes = [C.c_void_p]
+        L.rtb_closest_hit.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int] + [C.c_void_p] * 5 + [C.POINTER(Stats)]
+        L.rtb_closest_hit_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int] + [C.c_void_p] * 7
+        L.rtb_light_pdf.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.rtb_render.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.POINTER(Stats)]
+        L.rtb_render_device.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.rtb_resolve_device.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p]
+        L.rtb_write_ppm.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != RTB_OK:
+        raise RtbError(rc, lib().rtb_last_error().decode(errors="replace"))
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data_as(C.c_void_p)
+    if hasattr(a, "data_ptr"):      # torch tensor (host-pinned or device)
+        return C.c_void_p(a.data_ptr())
+    return C.c_void_p(int(a))
+
+
+def device_count():
+    return lib().rtb_device_count()
+
+
+def _np_view(ptr, shape, dtype):
+    n = int(np.prod(shape))
+    if n == 0 or not ptr:
+        return np.zeros(shape, dtype)
+    buf = (C.c_char * (n * np.dtype(dtype).itemsize)).from_address(ptr)
+    return np.frombuffer(buf, dtype=dtype).reshape(shape)
+
+
+class HostScene:
+    """Host-side scene (glTF load + BVH build on the C++ host): mirrors `Scene` after its constructor."""
+
+    def __init__(self, handle):
+        self.h = C.c_void_p(handle)
+        self.desc = SceneDesc()
+        _check(lib().rtb_host_scene_desc(self.h, C.byref(self.desc)))
+
+    @classmethod
+    def load_gltf(cls, path, width, height, samples):
+        h = C.c_void_p()
+        _check(lib().rtb_host_scene_load_gltf(str(path).encode(), width, height, samples, C.byref(h)))
+        return cls(h.value)
+
+    @classmethod
+    def from_triangles(cls, verts, normals=None, emissive_from=None, cam_pos=(0, 0, 30),
+                       cam_axes=((1, 0, 0), (0, 1, 0), (0, 0, -1)), fov=(0.7, 0.7), max_distance=1e9):
+        verts = np.ascontiguousarray(verts, np.float32).reshape(-1, 9)
+        n = verts.shape[0]
+        nrm = None if normals is None else np.ascontiguousarray(normals, np.float32).reshape(-1, 9)
+        pos = np.ascontiguousarray(cam_pos, np.float32)
+        axes = np.ascontiguousarray(cam_axes, np.float32).reshape(9)
+        h = C.c_void_p()
+        _check(lib().rtb_host_scene_from_triangles(_ptr(verts), _ptr(nrm), n, n if emissive_from is None else emissive_from,
+                                                   _ptr(pos), _ptr(axes), fov[0], fov[1], max_distance, C.byref(h)))
+        return cls(h.value)
+
+    def close(self):
+        if self.h:
+            lib().rtb_host_scene_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def build_seconds(self):
+        return lib().rtb_host_scene_build_seconds(self.h)
+
+    def bvh_stats(self):
+        n, c, m = C.c_uint64(), (C.c_uint64 * 5)(), C.c_uint64()
+        _check(lib().rtb_host_scene_bvh_stats(self.h, C.byref(n), C.byref(c), C.byref(m)))
+        return n.value, list(c), m.value
+
+    # numpy views into the host scene's arrays (valid while the HostScene lives)
+    def nodes(self):
+        d = self.desc
+        return _np_view(d.node_aabb, (d.n_nodes, 6), np.float32), _np_view(d.node_links, (d.n_nodes, 5), np.int32)
+
+    def light_nodes(self):
+        d = self.desc
+        return _np_view(d.light_node_aabb, (d.n_light_nodes, 6), np.float32), _np_view(d.light_node_links, (d.n_light_nodes, 5), np.int32)
+
+    def tris(self):
+        d = self.desc
+        n = d.n_tris
+        return dict(pos=_np_view(d.tri_pos, (n, 9), np.float32), nrm=_np_view(d.tri_nrm, (n, 9), np.float32),
+                    tan=_np_view(d.tri_tan, (n, 12), np.float32), uv=_np_view(d.tri_uv, (n, 6), np.float32),
+                    mesh=_np_view(d.tri_mesh, (n,), np.int32))
+
+    def light_pos(self):
+        return _np_view(self.desc.light_pos, (self.desc.n_lights, 9), np.float32)
+
+    def meshes(self):
+        d = self.desc
+        return _np_view(d.mesh_material, (d.n_meshes, 16), np.float32), _np_view(d.mesh_normal_transform, (d.n_meshes, 16), np.float64)
+
+    def textures(self):
+        out = []
+        for i in range(self.desc.n_textures):
+            t = self.desc.textures[i]
+            out.append(_np_view(t.rgba, (t.height, t.width, 4), np.uint8))
+        return out
+
+    def camera(self):
+        d = self.desc
+        return dict(pos=np.array(d.cam_pos[:], np.float32), axes=np.array(d.cam_axes[:], np.float32).reshape(3, 3),
+                    tan_half_fov=np.array(d.cam_tan_half_fov[:], np.float32), max_distance=d.max_distance, ray_depth=d.ray_depth)
+
+
+class Scene:
+    """Device-resident scene on one GPU; the drop-in for BVH::intersect and Scene::render."""
+
+    def __init__(self, host_scene_or_desc, device=0):
+        desc = host_scene_or_desc.desc if isinstance(host_scene_or_desc, HostScene) else host_scene_or_desc
+        self._keep = host_scene_or_desc
+        h = C.c_void_p()
+        _check(lib().rtb_scene_create(C.byref(desc), device, C.byref(h)))
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if self.h:
+            lib().rtb_scene_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def traversal_bytes(self):
+        return lib().rtb_scene_traversal_bytes(self.h)
+
+    def closest_hit(self, rays, cull=CULL_GLOBAL, counters=False, out=None):
+        """rays: (n,6) float32 host array (numpy or pinned torch).  Returns dict(id,t,u,v,inside,stats)."""
+        n = rays.shape[0]
+        if out is None:
+            out = dict(id=np.empty(n, np.int32), t=np.empty(n, np.float32), u=np.empty(n, np.float32),
+                       v=np.empty(n, np.float32), inside=np.empty(n, np.uint8))
+        st = Stats()
+        if counters:
+            st.box_tests = REQUEST_COUNTERS
+        _check(lib().rtb_closest_hit(self.h, _ptr(rays), n, cull, _ptr(out["id"]), _ptr(out.get("t")), _ptr(out.get("u")),
+                                     _ptr(out.get("v")), _ptr(out.get("inside")), C.byref(st)))
+        out = dict(out)
+        out["stats"] = st.as_dict()
+        return out
+
+    def closest_hit_device(self, d_rays, n, cull, d_id, d_t=None, d_u=None, d_v=None, d_inside=None, d_counters=None, stream=0):
+        _check(lib().rtb_closest_hit_device(self.h, _ptr(d_rays), n, cull, _ptr(d_id), _ptr(d_t), _ptr(d_u), _ptr(d_v),
+                                            _ptr(d_inside), _ptr(d_counters), C.c_void_p(stream)))
+
+    def light_pdf(self, rays):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        out = np.empty(rays.shape[0], np.float32)
+        _check(lib().rtb_light_pdf(self.h, _ptr(rays), rays.shape[0], _ptr(out)))
+        return out
+
+    def render(self, width, height, samples, rows=None, pixel0_seed=1, counters=False, want_accum=True, want_rgb=True,
+               accum=None, rgb=None):
+        r0, r1 = rows if rows is not None else (0, height)
+        p = RenderParams(width, height, samples, r0, r1, pixel0_seed, 0, 1 if counters else 0)
+        if accum is None and want_accum:
+            accum = np.empty((r1 - r0, width, 3), np.float32)
+        if rgb is None and want_rgb:
+            rgb = np.empty((r1 - r0, width, 3), np.uint8)
+        st = Stats()
+        _check(lib().rtb_render(self.h, C.byref(p), _ptr(accum), _ptr(rgb), C.byref(st)))
+        return dict(accum=accum, rgb=rgb, stats=st.as_dict())
+
+    def render_device(self, width, height, samples, rows, d_accum, d_rgb8=None, d_counters=None, pixel0_seed=1, counters=False, stream=0):
+        p = RenderParams(width, height, samples, rows[0], rows[1], pixel0_seed, 0, 1 if counters else 0)
+        _check(lib().rtb_render_device(self.h, C.byref(p), _ptr(d_accum), _ptr(d_rgb8), _ptr(d_counters), C.c_void_p(stream)))
+
+
+def resolve_device(d_accum, n_pixels, samples, d_rgb8, stream=0):
+    _check(lib().rtb_resolve_device(_ptr(d_accum), n_pixels, samples, _ptr(d_rgb8), C.c_void_p(stream)))
+
+
+def write_ppm(path, rgb):
+    rgb = np.ascontiguousarray(rgb, np.uint8)
+    _check(lib().rtb_write_ppm(str(path).encode(), rgb.shape[1], rgb.shape[0], _ptr(rgb)))

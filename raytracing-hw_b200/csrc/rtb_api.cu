@@ -1,0 +1,331 @@
+// Device half of the C ABI (include/rtb.h): scene upload (reference-order nodes -> 64-byte two-child nodes),
+// batched closest hit, light pdf, render.  No CPU fallback: every entry point needs a CUDA device.
+#include "../../include/rtb.h"
+#include "rtb_kernels.cuh"
+#include "rtb_layout.hpp"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace rtb {
+extern thread_local std::string g_last_error;   // host_api.cpp
+void set_error(const std::string &e);
+}  // namespace rtb
+
+#define RTB_CUDA(call)                                                                                              \
+    do {                                                                                                            \
+        cudaError_t e_ = (call);                                                                                    \
+        if (e_ != cudaSuccess) {                                                                                    \
+            rtb::set_error(std::string(#call) + ": " + cudaGetErrorString(e_));                                     \
+            return (e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver) ? RTB_ERR_NO_DEVICE : RTB_ERR_CUDA; \
+        }                                                                                                           \
+    } while (0)
+
+struct rtb_scene {
+    int device = 0;
+    rtb::DScene d;
+    std::vector<void *> allocs;
+    size_t traversal_bytes = 0;
+    cudaStream_t streams[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    // staging buffers reused across calls
+    void *stage = nullptr;
+    size_t stage_bytes = 0;
+    ~rtb_scene() {
+        cudaSetDevice(device);
+        for (void *p : allocs) cudaFree(p);
+        if (stage) cudaFree(stage);
+        for (auto &s : streams) if (s) cudaStreamDestroy(s);
+        for (auto &e : ev) if (e) cudaEventDestroy(e);
+    }
+};
+
+namespace {
+
+using namespace rtb;
+
+template <class T>
+int upload(rtb_scene *sc, const std::vector<T> &h, const T **out) {
+    *out = nullptr;
+    if (h.empty()) return RTB_OK;
+    void *p = nullptr;
+    RTB_CUDA(cudaMalloc(&p, h.size() * sizeof(T)));
+    sc->allocs.push_back(p);
+    RTB_CUDA(cudaMemcpy(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+    *out = (const T *) p;
+    return RTB_OK;
+}
+
+int upload_bvh(rtb_scene *sc, HostBvhOut &h, DBvh &d, uint32_t n_tris) {
+    int rc;
+    if ((rc = upload(sc, h.nodes, &d.nodes)) != RTB_OK) return rc;
+    if ((rc = upload(sc, h.tris, &d.tris)) != RTB_OK) return rc;
+    if ((rc = upload(sc, h.big, &d.big_leaves)) != RTB_OK) return rc;
+    fill_bvh_scalars(h, d, n_tris);
+    return RTB_OK;
+}
+
+int ensure_stage(rtb_scene *sc, size_t bytes) {
+    if (sc->stage_bytes >= bytes) return RTB_OK;
+    if (sc->stage) cudaFree(sc->stage);
+    sc->stage = nullptr;
+    sc->stage_bytes = 0;
+    RTB_CUDA(cudaMalloc(&sc->stage, bytes));
+    sc->stage_bytes = bytes;
+    return RTB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rtb_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
+    if (!desc || !out) { rtb::set_error("rtb_scene_create: null argument"); return RTB_ERR_INVALID; }
+    *out = nullptr;
+    const int ndev = rtb_device_count();
+    if (ndev <= 0) { rtb::set_error("no CUDA device available (this library has no CPU fallback)"); return RTB_ERR_NO_DEVICE; }
+    if (device < 0 || device >= ndev) { rtb::set_error("rtb_scene_create: device index out of range"); return RTB_ERR_INVALID; }
+    RTB_CUDA(cudaSetDevice(device));
+
+    rtb_scene *sc = new rtb_scene();
+    sc->device = device;
+    std::memset(&sc->d, 0, sizeof(sc->d));
+    auto fail = [&](int rc) { delete sc; return rc; };
+
+    std::string err;
+    HostLayout L;
+    if (!build_layout(desc, L, err)) {
+        rtb::set_error("rtb_scene_create: " + err);
+        return fail(RTB_ERR_INVALID);
+    }
+    int rc;
+    if ((rc = upload_bvh(sc, L.bvh, sc->d.bvh, desc->n_tris)) != RTB_OK) return fail(rc);
+    sc->traversal_bytes = L.bvh.nodes.size() * sizeof(DNode) + L.bvh.tris.size() * sizeof(float4);
+    if (desc->n_lights > 0) {
+        if ((rc = upload_bvh(sc, L.light_bvh, sc->d.light_bvh, desc->n_lights)) != RTB_OK) return fail(rc);
+        if ((rc = upload(sc, L.light_bvh.inv_area, &sc->d.light_inv_area)) != RTB_OK) return fail(rc);
+    }
+    if ((rc = upload(sc, L.shade, &sc->d.tri_shade)) != RTB_OK) return fail(rc);
+    if ((rc = upload(sc, L.tan, &sc->d.tri_tan)) != RTB_OK) return fail(rc);
+    if ((rc = upload(sc, L.material, &sc->d.mesh_material)) != RTB_OK) return fail(rc);
+    if ((rc = upload(sc, L.normal_transform, &sc->d.mesh_normal_transform)) != RTB_OK) return fail(rc);
+    sc->d.n_meshes = L.n_meshes;
+    {
+        std::vector<DTexture> tex(desc->n_textures);
+        for (uint32_t i = 0; i < desc->n_textures; ++i) {
+            const rtb_texture_desc &t = desc->textures[i];
+            const size_t bytes = (size_t) t.width * t.height * 4;
+            void *p = nullptr;
+            RTB_CUDA(cudaMalloc(&p, bytes));
+            sc->allocs.push_back(p);
+            RTB_CUDA(cudaMemcpy(p, t.rgba, bytes, cudaMemcpyHostToDevice));
+            tex[i] = {(const uchar4 *) p, t.width, t.height};
+        }
+        if ((rc = upload(sc, tex, &sc->d.textures)) != RTB_OK) return fail(rc);
+    }
+    fill_scalars(desc, sc->d);
+
+    for (auto &s : sc->streams) RTB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    for (auto &e : sc->ev) RTB_CUDA(cudaEventCreate(&e));
+    *out = sc;
+    return RTB_OK;
+}
+
+void rtb_scene_destroy(rtb_scene *scene) { delete scene; }
+int rtb_scene_device(const rtb_scene *scene) { return scene ? scene->device : -1; }
+size_t rtb_scene_traversal_bytes(const rtb_scene *scene) { return scene ? scene->traversal_bytes : 0; }
+
+int rtb_closest_hit_device(rtb_scene *scene, const float *d_rays6, size_t n, int cull_mode, int32_t *d_id, float *d_t, float *d_u,
+                           float *d_v, uint8_t *d_inside, unsigned long long *d_counters, void *stream) {
+    if (!scene || !d_rays6 || !d_id) { rtb::set_error("rtb_closest_hit_device: null argument"); return RTB_ERR_INVALID; }
+    if (cull_mode != RTB_CULL_REFERENCE && cull_mode != RTB_CULL_GLOBAL) { rtb::set_error("rtb_closest_hit_device: bad cull mode"); return RTB_ERR_INVALID; }
+    RTB_CUDA(cudaSetDevice(scene->device));
+    rtb::launch_closest_hit(scene->d, d_rays6, n, cull_mode, d_id, d_t, d_u, d_v, d_inside, d_counters, (cudaStream_t) stream);
+    RTB_CUDA(cudaGetLastError());
+    return RTB_OK;
+}
+
+// Host-pointer variant: the batch is cut into chunks that flow through three streams so that the host->device copy of
+// chunk k+1 and the device->host copy of chunk k-1 overlap the traversal of chunk k.
+int rtb_closest_hit(rtb_scene *scene, const float *rays6, size_t n, int cull_mode, int32_t *id, float *t, float *u, float *v,
+                    uint8_t *inside, rtb_stats *stats) {
+    if (!scene || !id || (n > 0 && !rays6)) { rtb::set_error("rtb_closest_hit: null argument"); return RTB_ERR_INVALID; }
+    if (cull_mode != RTB_CULL_REFERENCE && cull_mode != RTB_CULL_GLOBAL) { rtb::set_error("rtb_closest_hit: bad cull mode"); return RTB_ERR_INVALID; }
+    RTB_CUDA(cudaSetDevice(scene->device));
+    const bool count = stats != nullptr && stats->box_tests == RTB_REQUEST_COUNTERS;
+    if (stats) std::memset(stats, 0, sizeof(*stats));
+    if (n == 0) return RTB_OK;
+    const size_t chunk = std::min<size_t>(n, (size_t) 1 << 22);
+    const int nslots = 3;
+    const size_t per_ray = 24 + 4 + 4 + 4 + 4 + 1;
+    const size_t slot_bytes = ((chunk * per_ray + 255) / 256 + 8) * 256;
+    int rc = ensure_stage(scene, slot_bytes * nslots + 256);
+    if (rc != RTB_OK) return rc;
+    unsigned long long *d_cnt = nullptr;
+    if (count) {
+        d_cnt = (unsigned long long *) ((char *) scene->stage + slot_bytes * nslots);
+        RTB_CUDA(cudaMemsetAsync(d_cnt, 0, 16, scene->streams[0]));
+        RTB_CUDA(cudaStreamSynchronize(scene->streams[0]));
+    }
+    RTB_CUDA(cudaEventRecord(scene->ev[0], scene->streams[0]));
+    size_t launches = 0;
+    for (size_t off = 0, k = 0; off < n; off += chunk, ++k) {
+        const size_t m = std::min(chunk, n - off);
+        cudaStream_t st = scene->streams[k % nslots];
+        char *base = (char *) scene->stage + slot_bytes * (k % nslots);
+        float *d_rays = (float *) base;
+        int *d_id = (int *) (base + chunk * 24);
+        float *d_t = (float *) (base + chunk * 28);
+        float *d_u = (float *) (base + chunk * 32);
+        float *d_v = (float *) (base + chunk * 36);
+        uint8_t *d_in = (uint8_t *) (base + chunk * 40);
+        RTB_CUDA(cudaMemcpyAsync(d_rays, rays6 + off * 6, m * 24, cudaMemcpyHostToDevice, st));
+        rtb::launch_closest_hit(scene->d, d_rays, m, cull_mode, d_id, t ? d_t : nullptr, u ? d_u : nullptr, v ? d_v : nullptr,
+                                inside ? d_in : nullptr, d_cnt, st);
+        ++launches;
+        RTB_CUDA(cudaMemcpyAsync(id + off, d_id, m * 4, cudaMemcpyDeviceToHost, st));
+        if (t) RTB_CUDA(cudaMemcpyAsync(t + off, d_t, m * 4, cudaMemcpyDeviceToHost, st));
+        if (u) RTB_CUDA(cudaMemcpyAsync(u + off, d_u, m * 4, cudaMemcpyDeviceToHost, st));
+        if (v) RTB_CUDA(cudaMemcpyAsync(v + off, d_v, m * 4, cudaMemcpyDeviceToHost, st));
+        if (inside) RTB_CUDA(cudaMemcpyAsync(inside + off, d_in, m, cudaMemcpyDeviceToHost, st));
+    }
+    for (auto &s : scene->streams) RTB_CUDA(cudaStreamSynchronize(s));
+    RTB_CUDA(cudaEventRecord(scene->ev[1], scene->streams[0]));
+    RTB_CUDA(cudaEventSynchronize(scene->ev[1]));
+    RTB_CUDA(cudaGetLastError());
+    if (stats) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, scene->ev[0], scene->ev[1]);
+        stats->kernel_ms = ms;   // whole pipelined call (copies overlapped with traversal)
+        stats->closest_hit_rays = n;
+        stats->launches = launches;
+        if (count) {
+            unsigned long long c[2];
+            RTB_CUDA(cudaMemcpy(c, d_cnt, 16, cudaMemcpyDeviceToHost));
+            stats->box_tests = c[0];
+            stats->tri_tests = c[1];
+        }
+    }
+    return RTB_OK;
+}
+
+int rtb_light_pdf(rtb_scene *scene, const float *rays6, size_t n, float *pdf) {
+    if (!scene || !pdf || (n > 0 && !rays6)) { rtb::set_error("rtb_light_pdf: null argument"); return RTB_ERR_INVALID; }
+    RTB_CUDA(cudaSetDevice(scene->device));
+    if (n == 0) return RTB_OK;
+    int rc = ensure_stage(scene, n * 28 + 256);
+    if (rc != RTB_OK) return rc;
+    float *d_rays = (float *) scene->stage;
+    float *d_pdf = d_rays + n * 6;
+    cudaStream_t st = scene->streams[0];
+    RTB_CUDA(cudaMemcpyAsync(d_rays, rays6, n * 24, cudaMemcpyHostToDevice, st));
+    rtb::launch_light_pdf(scene->d, d_rays, n, d_pdf, st);
+    RTB_CUDA(cudaMemcpyAsync(pdf, d_pdf, n * 4, cudaMemcpyDeviceToHost, st));
+    RTB_CUDA(cudaStreamSynchronize(st));
+    RTB_CUDA(cudaGetLastError());
+    return RTB_OK;
+}
+
+int rtb_render_local_rows(const rtb_render_params *p) {
+    if (!p || p->width <= 0 || p->height <= 0 || p->row_begin < 0 || p->row_end > p->height || p->row_begin > p->row_end) return -1;
+    const int rows = p->row_end - p->row_begin;
+    if (p->interleave_count <= 1) return rows;
+    const int R = p->interleave_rows;
+    if (R <= 0 || R % 4 != 0 || p->interleave_index < 0 || p->interleave_index >= p->interleave_count) return -1;
+    const int blocks = (rows + R - 1) / R;
+    int local = 0;
+    for (int b = p->interleave_index; b < blocks; b += p->interleave_count) local += std::min(R, rows - b * R);
+    return local;
+}
+
+int rtb_render_global_row(const rtb_render_params *p, int lr) {
+    if (!p || lr < 0) return -1;
+    if (p->interleave_count <= 1) return p->row_begin + lr;
+    const int R = p->interleave_rows;
+    return p->row_begin + ((lr / R) * p->interleave_count + p->interleave_index) * R + lr % R;
+}
+
+int rtb_render_device(rtb_scene *scene, const rtb_render_params *p, float *d_accum, uint8_t *d_rgb8, unsigned long long *d_counters,
+                      void *stream) {
+    if (!scene || !p) { rtb::set_error("rtb_render_device: null argument"); return RTB_ERR_INVALID; }
+    const int local_rows = rtb_render_local_rows(p);
+    if (local_rows < 0 || p->samples <= 0) {
+        rtb::set_error("rtb_render_device: bad canvas / row range / interleave / sample count");
+        return RTB_ERR_INVALID;
+    }
+    if (p->sample_begin != 0) { rtb::set_error("rtb_render_device: sample_begin must be 0 (a pixel's samples share one sequential stream)"); return RTB_ERR_INVALID; }
+    RTB_CUDA(cudaSetDevice(scene->device));
+    rtb::RenderLaunch L;
+    L.width = p->width; L.height = p->height; L.samples = p->samples;
+    L.row_begin = p->row_begin; L.row_end = p->row_end;
+    L.il_count = p->interleave_count; L.il_index = p->interleave_index; L.il_rows = p->interleave_rows > 0 ? p->interleave_rows : 4;
+    L.local_rows = local_rows;
+    L.pixel0_seed = p->pixel0_seed;
+    L.d_accum = d_accum; L.d_rgb8 = d_rgb8; L.d_counters = d_counters;
+    L.count_tests = (p->flags & RTB_RENDER_COUNTERS) != 0 && d_counters != nullptr;
+    L.cull_mode = (p->flags & RTB_RENDER_REFERENCE_CULL) ? RTB_CULL_REFERENCE : RTB_CULL_GLOBAL;
+    rtb::launch_render(scene->d, L, (cudaStream_t) stream);
+    RTB_CUDA(cudaGetLastError());
+    return RTB_OK;
+}
+
+int rtb_render(rtb_scene *scene, const rtb_render_params *p, float *accum, uint8_t *rgb8, rtb_stats *stats) {
+    if (!scene || !p) { rtb::set_error("rtb_render: null argument"); return RTB_ERR_INVALID; }
+    if (stats) std::memset(stats, 0, sizeof(*stats));
+    RTB_CUDA(cudaSetDevice(scene->device));
+    const int local_rows = rtb_render_local_rows(p);
+    if (local_rows < 0) { rtb::set_error("rtb_render: bad canvas / row range / interleave"); return RTB_ERR_INVALID; }
+    const size_t npix = (size_t) local_rows * (size_t) p->width;
+    const size_t accum_bytes = npix * 3 * sizeof(float), rgb_bytes = npix * 3;
+    const size_t rgb_off = (accum_bytes + 255) / 256 * 256, cnt_off = rgb_off + (rgb_bytes + 255) / 256 * 256;
+    int rc = ensure_stage(scene, cnt_off + 256);
+    if (rc != RTB_OK) return rc;
+    char *base = (char *) scene->stage;
+    float *d_accum = (float *) base;
+    uint8_t *d_rgb = (uint8_t *) (base + rgb_off);
+    unsigned long long *d_cnt = (unsigned long long *) (base + cnt_off);
+    cudaStream_t st = scene->streams[0];
+    RTB_CUDA(cudaMemsetAsync(d_cnt, 0, 32, st));
+    RTB_CUDA(cudaEventRecord(scene->ev[0], st));
+    rc = rtb_render_device(scene, p, d_accum, rgb8 ? d_rgb : nullptr, d_cnt, st);
+    if (rc != RTB_OK) return rc;
+    RTB_CUDA(cudaEventRecord(scene->ev[1], st));
+    if (accum && accum_bytes) RTB_CUDA(cudaMemcpyAsync(accum, d_accum, accum_bytes, cudaMemcpyDeviceToHost, st));
+    if (rgb8 && rgb_bytes) RTB_CUDA(cudaMemcpyAsync(rgb8, d_rgb, rgb_bytes, cudaMemcpyDeviceToHost, st));
+    unsigned long long c[4] = {0, 0, 0, 0};
+    RTB_CUDA(cudaMemcpyAsync(c, d_cnt, 32, cudaMemcpyDeviceToHost, st));
+    RTB_CUDA(cudaStreamSynchronize(st));
+    RTB_CUDA(cudaGetLastError());
+    if (stats) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, scene->ev[0], scene->ev[1]);
+        stats->kernel_ms = ms;
+        stats->closest_hit_rays = c[0];
+        stats->light_pdf_queries = c[1];
+        stats->box_tests = c[2];
+        stats->tri_tests = c[3];
+        stats->launches = npix ? 1 : 0;
+    }
+    return RTB_OK;
+}
+
+int rtb_resolve_device(const float *d_accum, size_t n_pixels, int samples, uint8_t *d_rgb8, void *stream) {
+    if (!d_accum || !d_rgb8 || samples <= 0) { rtb::set_error("rtb_resolve_device: invalid argument"); return RTB_ERR_INVALID; }
+    rtb::launch_resolve(d_accum, n_pixels, samples, d_rgb8, (cudaStream_t) stream);
+    RTB_CUDA(cudaGetLastError());
+    return RTB_OK;
+}
+
+}  // extern "C"

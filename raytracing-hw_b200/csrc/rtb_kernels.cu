@@ -1,0 +1,86 @@
+// Batched closest-hit and light-pdf kernels (sm_100a).  One ray per thread, per-thread traversal stack in local
+// memory, node = 4 x LDG.128, triangle = 3 x LDG.128 through the read-only path.
+// Compiled with --fmad=false (decision-exact float arithmetic, see rtb_device.cuh).
+#include "rtb_kernels.cuh"
+#include "rtb_shade.cuh"
+
+namespace rtb {
+
+// Replaces BVH::intersect (src/core/bvh.cpp:239-243) for a batch.
+template <int CULL, bool COUNT>
+__global__ void __launch_bounds__(128) k_closest_hit(const __grid_constant__ DScene sc, const float *__restrict__ rays6, size_t n,
+                                                     int *__restrict__ id, float *__restrict__ t, float *__restrict__ u,
+                                                     float *__restrict__ v, uint8_t *__restrict__ inside,
+                                                     unsigned long long *__restrict__ counters) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    Counters cnt = {0ull, 0ull};
+    if (i < n) {
+        const float2 *rp = reinterpret_cast<const float2 *>(rays6 + i * 6);
+        const float2 r0 = __ldg(rp), r1 = __ldg(rp + 1), r2 = __ldg(rp + 2);
+        Ray r;
+        make_ray(r, r0.x, r0.y, r1.x, r1.y, r2.x, r2.y);
+        Hit h;
+        const bool ok = closest_hit<CULL, COUNT>(sc.bvh, r, h, &cnt);
+        id[i] = ok ? h.id : -1;
+        if (t) t[i] = ok ? h.t : 0.f;
+        if (u) u[i] = ok ? h.u : 0.f;
+        if (v) v[i] = ok ? h.v : 0.f;
+        if (inside) {
+            uint8_t in = 0;
+            if (ok) {
+                // `if (dot(ray.direction, normal) > 0) inside = true` (primitive.cpp:51-54)
+                const float4 q2 = __ldg(sc.bvh.tris + (size_t) h.id * 3 + 2);
+                float dn = r.d[0] * q2.y;
+                dn = dn + r.d[1] * q2.z;
+                dn = dn + r.d[2] * q2.w;
+                in = dn > 0.f ? 1 : 0;
+            }
+            inside[i] = in;
+        }
+    }
+    if (COUNT) {
+        // warp-aggregate, then one atomic per warp and counter
+        for (int o = 16; o > 0; o >>= 1) {
+            cnt.box += __shfl_down_sync(0xffffffffu, cnt.box, o);
+            cnt.tri += __shfl_down_sync(0xffffffffu, cnt.tri, o);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(&counters[0], cnt.box);
+            atomicAdd(&counters[1], cnt.tri);
+        }
+    }
+}
+
+void launch_closest_hit(const DScene &sc, const float *d_rays6, size_t n, int cull_mode, int *d_id, float *d_t, float *d_u,
+                        float *d_v, uint8_t *d_inside, unsigned long long *d_counters, cudaStream_t stream) {
+    if (n == 0) return;
+    const unsigned block = 128;
+    const unsigned grid = (unsigned) ((n + block - 1) / block);
+    const bool count = d_counters != nullptr;
+    if (cull_mode == 0) {
+        if (count) k_closest_hit<0, true><<<grid, block, 0, stream>>>(sc, d_rays6, n, d_id, d_t, d_u, d_v, d_inside, d_counters);
+        else k_closest_hit<0, false><<<grid, block, 0, stream>>>(sc, d_rays6, n, d_id, d_t, d_u, d_v, d_inside, d_counters);
+    } else {
+        if (count) k_closest_hit<1, true><<<grid, block, 0, stream>>>(sc, d_rays6, n, d_id, d_t, d_u, d_v, d_inside, d_counters);
+        else k_closest_hit<1, false><<<grid, block, 0, stream>>>(sc, d_rays6, n, d_id, d_t, d_u, d_v, d_inside, d_counters);
+    }
+}
+
+// ManyLightsDistribution::pdf (src/utils/random.cpp:179-188) for a batch of (point, direction).
+__global__ void __launch_bounds__(128) k_light_pdf(const __grid_constant__ DScene sc, const float *__restrict__ rays6, size_t n,
+                                                   float *__restrict__ pdf) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *rp = rays6 + i * 6;
+    float prob = 0.f;
+    if (sc.n_lights > 0) prob = pdf_lights<false>(sc, V3{rp[0], rp[1], rp[2]}, V3{rp[3], rp[4], rp[5]}, nullptr);
+    pdf[i] = prob;
+}
+
+void launch_light_pdf(const DScene &sc, const float *d_rays6, size_t n, float *d_pdf, cudaStream_t stream) {
+    if (n == 0) return;
+    const unsigned block = 128;
+    k_light_pdf<<<(unsigned) ((n + block - 1) / block), block, 0, stream>>>(sc, d_rays6, n, d_pdf);
+}
+
+}  // namespace rtb

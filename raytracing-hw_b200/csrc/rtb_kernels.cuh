@@ -1,0 +1,27 @@
+// Kernel launchers (defined in rtb_kernels.cu / rtb_integrator.cu), called by the C ABI in rtb_api.cu.
+#pragma once
+#include "rtb_device.cuh"
+
+namespace rtb {
+
+void launch_closest_hit(const DScene &sc, const float *d_rays6, size_t n, int cull_mode, int *d_id, float *d_t, float *d_u,
+                        float *d_v, uint8_t *d_inside, unsigned long long *d_counters, cudaStream_t stream);
+
+void launch_light_pdf(const DScene &sc, const float *d_rays6, size_t n, float *d_pdf, cudaStream_t stream);
+
+struct RenderLaunch {
+    int width, height, samples;
+    int row_begin, row_end;
+    int il_count, il_index, il_rows;    // row-block interleave (il_count <= 1: contiguous); see rtb_render_params
+    int local_rows;                     // rows this launch renders
+    unsigned pixel0_seed;
+    float *d_accum;                     // (row_end-row_begin) x width x 3, may be null
+    uint8_t *d_rgb8;                    // same extent, may be null
+    unsigned long long *d_counters;     // 4 x u64 {rays, light queries, box, tri} or null
+    bool count_tests;                   // also count box / triangle tests (slower instantiation)
+    int cull_mode;                      // RTB_CULL_*
+};
+void launch_render(const DScene &sc, const RenderLaunch &p, cudaStream_t stream);
+void launch_resolve(const float *d_accum, size_t n_pixels, int samples, uint8_t *d_rgb8, cudaStream_t stream);
+
+}  // namespace rtb

@@ -1,0 +1,171 @@
+// Host half of the C ABI (include/rtb.h): glTF load + BVH build -> rtb_scene_desc, PPM writer.
+#include "../../include/rtb.h"
+#include "host_scene.h"
+
+#include <cmath>
+#include <cstring>
+#include <fstream>
+#include <string>
+
+struct rtb_host_scene {
+    rtb::HostScene s;
+    std::vector<rtb_texture_desc> tex_desc;
+};
+
+namespace rtb {
+thread_local std::string g_last_error;
+void set_error(const std::string &e) { g_last_error = e; }
+}  // namespace rtb
+
+extern "C" {
+
+const char *rtb_last_error(void) { return rtb::g_last_error.c_str(); }
+
+int rtb_host_scene_load_gltf(const char *path, int width, int height, int samples, rtb_host_scene **out) {
+    if (!path || !out || width <= 0 || height <= 0 || samples <= 0) {
+        rtb::set_error("rtb_host_scene_load_gltf: invalid argument");
+        return RTB_ERR_INVALID;
+    }
+    rtb_host_scene *hs = new rtb_host_scene();
+    try {
+        rtb::load_gltf(path, width, height, samples, hs->s);
+        hs->s.finalize();
+    } catch (const std::exception &e) {
+        rtb::set_error(e.what());
+        delete hs;
+        return RTB_ERR_IO;
+    }
+    *out = hs;
+    return RTB_OK;
+}
+
+int rtb_host_scene_from_triangles(const float *verts9, const float *nrm9, size_t n, size_t emissive_from,
+                                  const float cam_pos[3], const float cam_axes[9], float fov_x, float fov_y,
+                                  float max_distance, rtb_host_scene **out) {
+    if (!verts9 || !out || n == 0 || !cam_pos || !cam_axes) {
+        rtb::set_error("rtb_host_scene_from_triangles: invalid argument");
+        return RTB_ERR_INVALID;
+    }
+    rtb_host_scene *hs = new rtb_host_scene();
+    rtb::HostScene &s = hs->s;
+    try {
+        s.tris.resize(n);
+        for (size_t i = 0; i < n; ++i) {
+            const float *v = verts9 + i * 9;
+            float *o = &s.tris.pos[i * 9];
+            for (int k = 0; k < 3; ++k) {
+                o[k] = v[k];
+                o[3 + k] = v[3 + k] + (-v[k]);
+                o[6 + k] = v[6 + k] + (-v[k]);
+            }
+            if (nrm9) {
+                std::memcpy(&s.tris.nrm[i * 9], nrm9 + i * 9, 36);
+            } else {   // normal(cross(U, V)) (vector.h:169-174, 372-378)
+                const float *U = o + 3, *V = o + 6;
+                float c[3] = {U[1] * V[2] - V[1] * U[2], U[2] * V[0] - V[2] * U[0], U[0] * V[1] - V[0] * U[1]};
+                float mod = 0.f;
+                for (int k = 0; k < 3; ++k) mod += c[k] * c[k];
+                mod = 1.f / std::sqrt(mod);
+                for (int v3 = 0; v3 < 3; ++v3)
+                    for (int k = 0; k < 3; ++k) s.tris.nrm[i * 9 + v3 * 3 + k] = c[k] * mod;
+            }
+            s.tris.mesh[i] = (i >= emissive_from) ? 1 : 0;
+        }
+        const float m0[16] = {1.f, 1.f, 1.f, 1.f, 1.f, 0.f, 0.f, 0.f, 0.f, 1.f, -1.f, -1.f, -1.f, -1.f, 0.f, 0.f};
+        float m1[16];
+        std::memcpy(m1, m0, sizeof(m0));
+        m1[5] = m1[6] = m1[7] = 1.f;
+        s.mesh_material.insert(s.mesh_material.end(), m0, m0 + 16);
+        s.mesh_material.insert(s.mesh_material.end(), m1, m1 + 16);
+        const double I[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+        for (int r = 0; r < 2; ++r) s.mesh_normal_transform.insert(s.mesh_normal_transform.end(), I, I + 16);
+        std::memcpy(s.cam_pos, cam_pos, 12);
+        std::memcpy(s.cam_axes, cam_axes, 36);
+        s.cam_fov[0] = fov_x;
+        s.cam_fov[1] = fov_y;
+        s.cam_tan_half_fov[0] = std::tan(fov_x / 2);
+        s.cam_tan_half_fov[1] = std::tan(fov_y / 2);
+        s.max_distance = max_distance;
+        s.finalize();
+    } catch (const std::exception &e) {
+        rtb::set_error(e.what());
+        delete hs;
+        return RTB_ERR_INVALID;
+    }
+    *out = hs;
+    return RTB_OK;
+}
+
+int rtb_host_scene_desc(const rtb_host_scene *hs_c, rtb_scene_desc *d) {
+    if (!hs_c || !d) {
+        rtb::set_error("rtb_host_scene_desc: invalid argument");
+        return RTB_ERR_INVALID;
+    }
+    rtb_host_scene *hs = const_cast<rtb_host_scene *>(hs_c);
+    const rtb::HostScene &s = hs->s;
+    std::memset(d, 0, sizeof(*d));
+    d->n_nodes = (uint32_t) s.bvh.size();
+    d->node_aabb = s.bvh.aabb.data();
+    d->node_links = s.bvh.links.data();
+    d->n_tris = (uint32_t) s.tris.size();
+    d->tri_pos = s.tris.pos.data();
+    d->tri_nrm = s.tris.nrm.data();
+    d->tri_tan = s.tris.tan.data();
+    d->tri_uv = s.tris.uv.data();
+    d->tri_mesh = s.tris.mesh.data();
+    d->n_meshes = (uint32_t) s.n_meshes();
+    d->mesh_material = s.mesh_material.data();
+    d->mesh_normal_transform = s.mesh_normal_transform.data();
+    hs->tex_desc.resize(s.textures.size());
+    for (size_t i = 0; i < s.textures.size(); ++i)
+        hs->tex_desc[i] = {s.textures[i].width, s.textures[i].height, s.textures[i].rgba.data()};
+    d->n_textures = (uint32_t) s.textures.size();
+    d->textures = hs->tex_desc.data();
+    d->n_lights = (uint32_t) s.lights.size();
+    d->light_pos = s.lights.pos.data();
+    d->n_light_nodes = (uint32_t) s.light_bvh.size();
+    d->light_node_aabb = s.light_bvh.aabb.data();
+    d->light_node_links = s.light_bvh.links.data();
+    std::memcpy(d->cam_pos, s.cam_pos, 12);
+    std::memcpy(d->cam_axes, s.cam_axes, 36);
+    d->cam_tan_half_fov[0] = s.cam_tan_half_fov[0];
+    d->cam_tan_half_fov[1] = s.cam_tan_half_fov[1];
+    d->ray_depth = s.ray_depth;
+    d->max_distance = s.max_distance;
+    d->bg_color[0] = d->bg_color[1] = d->bg_color[2] = 0.f;
+    return RTB_OK;
+}
+
+int rtb_host_scene_bvh_stats(const rtb_host_scene *hs, uint64_t *n_nodes, uint64_t counts5[5], uint64_t *max_leaf) {
+    if (!hs) return RTB_ERR_INVALID;
+    const rtb::HostBvh &b = hs->s.bvh;
+    uint64_t c[5] = {0, 0, 0, 0, 0}, mx = 0;
+    for (size_t i = 0; i < b.size(); ++i) {
+        const uint64_t k = (uint64_t) b.links[i * 5 + 4];
+        if (k < 5) ++c[k];
+        if (k > mx) mx = k;
+    }
+    if (n_nodes) *n_nodes = b.size();
+    if (counts5) std::memcpy(counts5, c, sizeof(c));
+    if (max_leaf) *max_leaf = mx;
+    return RTB_OK;
+}
+
+double rtb_host_scene_build_seconds(const rtb_host_scene *hs) { return hs ? hs->s.build_seconds : 0.0; }
+
+void rtb_host_scene_destroy(rtb_host_scene *hs) { delete hs; }
+
+int rtb_write_ppm(const char *path, int width, int height, const uint8_t *rgb8) {
+    if (!path || !rgb8 || width <= 0 || height <= 0) return RTB_ERR_INVALID;
+    std::ofstream out(path, std::ios_base::binary);
+    if (!out) {
+        rtb::set_error("File open error");   // canvas.h:79-80
+        return RTB_ERR_IO;
+    }
+    out << "P6\n" << width << " " << height << "\n" << "255" << "\n";
+    out.write((const char *) rgb8, (std::streamsize) width * height * 3);
+    out.close();
+    return out ? RTB_OK : RTB_ERR_IO;
+}
+
+}  // extern "C"

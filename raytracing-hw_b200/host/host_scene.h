@@ -1,0 +1,69 @@
+// Host-side flat scene: what Scene holds after its constructor (src/core/scene.cpp:197-249), as SoA arrays that
+// map 1:1 onto rtb_scene_desc (include/rtb.h).  glTF loading and BVH construction stay on the host (north_star).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace rtb {
+
+struct HostTexture {
+    int width = 0, height = 0;
+    std::vector<uint8_t> rgba;   // always 4 channels (tinygltf expands every image, tiny_gltf.h:2609,2681-2683)
+};
+
+// struct Node (src/core/bvh.h:10-17) flattened: aabb min/max + {left,right,split_dim,first,count}, -1 = invalidKey
+struct HostBvh {
+    std::vector<float> aabb;      // n x 6
+    std::vector<int32_t> links;   // n x 5
+    size_t size() const { return links.size() / 5; }
+};
+
+// struct Primitive (src/geometry/primitive.h:96-134) as SoA
+struct HostTriangles {
+    std::vector<float> pos;   // n x 9 : p0, U, V
+    std::vector<float> nrm;   // n x 9
+    std::vector<float> tan;   // n x 12
+    std::vector<float> uv;    // n x 6
+    std::vector<int32_t> mesh;
+    size_t size() const { return mesh.size(); }
+    void resize(size_t n) {
+        pos.resize(n * 9); nrm.resize(n * 9); tan.resize(n * 12); uv.resize(n * 6); mesh.resize(n);
+    }
+    void permute(const std::vector<uint32_t> &order);   // new[i] = old[order[i]]
+};
+
+struct HostScene {
+    HostTriangles tris;          // post-build order once build() ran
+    HostBvh bvh;
+    std::vector<float> mesh_material;              // n x 16 (layout in rtb.h)
+    std::vector<double> mesh_normal_transform;     // n x 16
+    std::vector<HostTexture> textures;
+    HostTriangles lights;        // emissive triangles, re-ordered by the light BVH (random.cpp:156-167)
+    HostBvh light_bvh;
+    float cam_pos[3] = {0, 0, 0};
+    float cam_axes[9] = {1, 0, 0, 0, 1, 0, 0, 0, -1};
+    float cam_fov[2] = {0.7f, 0.7f};
+    float cam_tan_half_fov[2] = {0, 0};
+    int width = 0, height = 0, samples = 0;
+    int ray_depth = 6;           // src/io/scene_parser.cpp:17
+    float max_distance = 1e9f;   // src/io/scene_parser.cpp:22
+    double build_seconds = 0.0;
+    std::vector<std::string> warnings;
+
+    size_t n_meshes() const { return mesh_material.size() / 16; }
+    // Scene::Scene (src/core/scene.cpp:197-249): BVH over all triangles, then the emissive copy + its BVH.
+    void finalize();
+};
+
+// BVH::buildBVH (src/core/bvh.cpp:5-175): widest-axis full-sweep SAH, leaf <= 4, libstdc++ sort/partition order.
+// Reorders `tris` in place exactly as the reference reorders Scene::objects.  threads<=1: sequential.
+void build_bvh(HostTriangles &tris, HostBvh &out, int threads = 0);
+
+// parse_scene_gltf (src/io/scene_parser.cpp:25-350); throws std::runtime_error like the reference.
+void load_gltf(const std::string &path, int width, int height, int samples, HostScene &scene);
+
+// PNG (own decoder, zlib) -> RGBA8.  JPEG is supported only when the build found stb_image.h (RTB_HAVE_STB).
+bool decode_image(const std::vector<uint8_t> &bytes, HostTexture &out, std::string &err);
+
+}  // namespace rtb

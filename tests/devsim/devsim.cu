@@ -1,0 +1,135 @@
+// CPU-side debugging harness: the device functions of raytracing-hw_b200/csrc/*.cuh compiled for the HOST by nvcc,
+// driven over host arrays.  Lets the decision-exact restatement be checked against the reference in a container
+// without a GPU (tests/test_devsim.py).  TEST TOOLING ONLY: librtb.so neither links nor calls this, and nothing
+// here is a fallback for the C ABI (which fails with RTB_ERR_NO_DEVICE when no GPU is usable).
+#include "../../raytracing-hw_b200/csrc/rtb_layout.hpp"
+
+#include <omp.h>
+
+using namespace rtb;
+
+namespace {
+struct SimScene {
+    HostLayout L;
+    std::vector<DTexture> tex;
+    DScene d;
+};
+
+bool make_scene(const rtb_scene_desc *desc, SimScene &s, std::string &err) {
+    std::memset(&s.d, 0, sizeof(s.d));
+    if (!build_layout(desc, s.L, err)) return false;
+    auto bind = [](HostBvhOut &h, DBvh &d, uint32_t n) {
+        d.nodes = h.nodes.data();
+        d.tris = h.tris.data();
+        d.big_leaves = h.big.data();
+        fill_bvh_scalars(h, d, n);
+    };
+    bind(s.L.bvh, s.d.bvh, desc->n_tris);
+    if (desc->n_lights) {
+        bind(s.L.light_bvh, s.d.light_bvh, desc->n_lights);
+        s.d.light_inv_area = s.L.light_bvh.inv_area.data();
+    }
+    s.d.tri_shade = s.L.shade.data();
+    s.d.tri_tan = s.L.tan.empty() ? nullptr : s.L.tan.data();
+    s.d.mesh_material = s.L.material.data();
+    s.d.mesh_normal_transform = s.L.normal_transform.data();
+    s.d.n_meshes = s.L.n_meshes;
+    s.tex.resize(desc->n_textures);
+    for (uint32_t i = 0; i < desc->n_textures; ++i)
+        s.tex[i] = {(const uchar4 *) desc->textures[i].rgba, desc->textures[i].width, desc->textures[i].height};
+    s.d.textures = s.tex.data();
+    fill_scalars(desc, s.d);
+    return true;
+}
+std::string g_err;
+}  // namespace
+
+extern "C" {
+
+const char *devsim_last_error() { return g_err.c_str(); }
+
+int devsim_closest_hit(const rtb_scene_desc *desc, const float *rays6, size_t n, int cull, int32_t *id, float *t, float *u, float *v,
+                       uint8_t *inside, unsigned long long *counters2) {
+    SimScene s;
+    if (!make_scene(desc, s, g_err)) return 1;
+    unsigned long long box = 0, tri = 0;
+#pragma omp parallel for schedule(dynamic, 1024) reduction(+ : box, tri)
+    for (size_t i = 0; i < n; ++i) {
+        Ray r;
+        make_ray(r, rays6[i * 6], rays6[i * 6 + 1], rays6[i * 6 + 2], rays6[i * 6 + 3], rays6[i * 6 + 4], rays6[i * 6 + 5]);
+        Hit h;
+        Counters c = {0, 0};
+        const bool ok = cull == 0 ? closest_hit<0, true>(s.d.bvh, r, h, &c) : closest_hit<1, true>(s.d.bvh, r, h, &c);
+        box += c.box;
+        tri += c.tri;
+        id[i] = ok ? h.id : -1;
+        if (t) t[i] = ok ? h.t : 0.f;
+        if (u) u[i] = ok ? h.u : 0.f;
+        if (v) v[i] = ok ? h.v : 0.f;
+        if (inside) {
+            uint8_t in = 0;
+            if (ok) {
+                const float4 q2 = s.d.bvh.tris[(size_t) h.id * 3 + 2];
+                in = dot(V3{r.d[0], r.d[1], r.d[2]}, V3{q2.y, q2.z, q2.w}) > 0.f ? 1 : 0;
+            }
+            inside[i] = in;
+        }
+    }
+    if (counters2) { counters2[0] = box; counters2[1] = tri; }
+    return 0;
+}
+
+int devsim_light_pdf(const rtb_scene_desc *desc, const float *rays6, size_t n, float *pdf) {
+    SimScene s;
+    if (!make_scene(desc, s, g_err)) return 1;
+    for (size_t i = 0; i < n; ++i) {
+        const float *rp = rays6 + i * 6;
+        pdf[i] = s.d.n_lights ? pdf_lights<false>(s.d, V3{rp[0], rp[1], rp[2]}, V3{rp[3], rp[4], rp[5]}, nullptr) : 0.f;
+    }
+    return 0;
+}
+
+int devsim_render(const rtb_scene_desc *desc, const rtb_render_params *p, float *accum, uint8_t *rgb8, unsigned long long *counters4) {
+    SimScene s;
+    if (!make_scene(desc, s, g_err)) return 1;
+    const int cull = (p->flags & RTB_RENDER_REFERENCE_CULL) ? 0 : 1;
+    unsigned long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+    const int rows = p->row_end - p->row_begin;
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : c0, c1, c2, c3)
+    for (int lr = 0; lr < rows; ++lr) {
+        const int py = p->row_begin + lr;
+        for (int px = 0; px < p->width; ++px) {
+            PathCounters pc = {0, 0, {0, 0}};
+            const V3 sum = cull == 0 ? render_pixel<0, true>(s.d, px, py, p->width, p->height, p->samples, p->pixel0_seed, &pc)
+                                     : render_pixel<1, true>(s.d, px, py, p->width, p->height, p->samples, p->pixel0_seed, &pc);
+            c0 += pc.rays; c1 += pc.light_queries; c2 += pc.tests.box; c3 += pc.tests.tri;
+            const size_t o = ((size_t) lr * p->width + px) * 3;
+            if (accum) { accum[o] = sum.x; accum[o + 1] = sum.y; accum[o + 2] = sum.z; }
+            if (rgb8) {
+                const float nz = 1.f / (float) p->samples;
+                rgb8[o] = resolve_channel(sum.x, nz);
+                rgb8[o + 1] = resolve_channel(sum.y, nz);
+                rgb8[o + 2] = resolve_channel(sum.z, nz);
+            }
+        }
+    }
+    if (counters4) { counters4[0] = c0; counters4[1] = c1; counters4[2] = c2; counters4[3] = c3; }
+    return 0;
+}
+
+// one path for an explicit ray and engine seed (mirror of oracle/ref_harness.cpp: ref_trace_path)
+int devsim_trace_path(const rtb_scene_desc *desc, const float *o3, const float *d3, unsigned engine_seed, float *rgb3, unsigned *engine_after) {
+    SimScene s;
+    if (!make_scene(desc, s, g_err)) return 1;
+    Rng g;
+    rng_seed(g, engine_seed);
+    Ray r;
+    make_ray(r, o3[0], o3[1], o3[2], d3[0], d3[1], d3[2]);
+    PathCounters pc = {0, 0, {0, 0}};
+    const V3 c = trace_path<0, false>(s.d, r, g, &pc);
+    rgb3[0] = c.x; rgb3[1] = c.y; rgb3[2] = c.z;
+    *engine_after = g.x;
+    return 0;
+}
+
+}  // extern "C"
