@@ -268,20 +268,26 @@ class Scene:
         return out
 
     def render(self, width, height, samples, rows=None, pixel0_seed=1, counters=False, want_accum=True, want_rgb=True,
-               accum=None, rgb=None):
-        r0, r1 = rows if rows is not None else (0, height)
-        p = RenderParams(width, height, samples, r0, r1, pixel0_seed, 0, 1 if counters else 0)
+               accum=None, rgb=None, reference_cull=False, params=None):
+        """Replaces Scene::render.  HOST output buffers (numpy or pinned torch); copies are inside the call."""
+        if params is None:
+            r0, r1 = rows if rows is not None else (0, height)
+            flags = (1 if counters else 0) | (2 if reference_cull else 0)
+            params = RenderParams(width, height, samples, r0, r1, pixel0_seed, 0, flags)
+        n = lib().rtb_render_local_rows(C.byref(params))
+        if n < 0:
+            raise RtbError(RTB_ERR_INVALID, "bad render parameters")
         if accum is None and want_accum:
-            accum = np.empty((r1 - r0, width, 3), np.float32)
+            accum = np.empty((n, params.width, 3), np.float32)
         if rgb is None and want_rgb:
-            rgb = np.empty((r1 - r0, width, 3), np.uint8)
+            rgb = np.empty((n, params.width, 3), np.uint8)
         st = Stats()
-        _check(lib().rtb_render(self.h, C.byref(p), _ptr(accum), _ptr(rgb), C.byref(st)))
+        _check(lib().rtb_render(self.h, C.byref(params), _ptr(accum), _ptr(rgb), C.byref(st)))
         return dict(accum=accum, rgb=rgb, stats=st.as_dict())
 
-    def render_device(self, width, height, samples, rows, d_accum, d_rgb8=None, d_counters=None, pixel0_seed=1, counters=False, stream=0):
-        p = RenderParams(width, height, samples, rows[0], rows[1], pixel0_seed, 0, 1 if counters else 0)
-        _check(lib().rtb_render_device(self.h, C.byref(p), _ptr(d_accum), _ptr(d_rgb8), _ptr(d_counters), C.c_void_p(stream)))
+    def render_device(self, params, d_accum=None, d_rgb8=None, d_counters=None, stream=0):
+        """DEVICE output pointers (e.g. torch tensors), asynchronous on `stream` (a cudaStream_t handle)."""
+        _check(lib().rtb_render_device(self.h, C.byref(params), _ptr(d_accum), _ptr(d_rgb8), _ptr(d_counters), C.c_void_p(stream)))
 
 
 def resolve_device(d_accum, n_pixels, samples, d_rgb8, stream=0):

@@ -1,0 +1,85 @@
+"""CPU-side check of the restated device arithmetic: the device headers (raytracing-hw_b200/csrc/*.cuh) compiled
+for the host by nvcc (tests/devsim/) against the reference's golden answers.  This is NOT the parity proof of the
+CUDA path (that is tests/test_gpu_*.py, on the B200) -- it catches restatement errors where no GPU exists."""
+import numpy as np
+import pytest
+
+import _util
+
+rtb = _util.rtb
+SCENES = _util.SMALL_SCENES + ["sponza_small"]
+
+
+@pytest.mark.parametrize("name", SCENES)
+@pytest.mark.parametrize("cull", [rtb.CULL_REFERENCE, rtb.CULL_GLOBAL])
+def test_closest_hit_bit_exact(name, cull, host_scene):
+    g = _util.load_golden(name)
+    hs = host_scene(name)
+    rays = _util.box_rays(g["root_box"], g["hit_id"].shape[0], seed=1000)
+    h = _util.devsim_closest_hit(hs, rays, cull)
+    assert np.array_equal(h["id"], g["hit_id"])
+    for k in ("t", "u", "v", "inside"):
+        assert np.array_equal(h[k], g["hit_" + k]), k
+    h = _util.devsim_closest_hit(hs, _util.camera_rays(_util.golden_camera(g), g["cam_hit_id"].shape[0], seed=2000), cull)
+    assert np.array_equal(h["id"], g["cam_hit_id"]) and np.array_equal(h["t"], g["cam_hit_t"])
+
+
+@pytest.mark.parametrize("name", ["s6_1", "soup_10k"])
+def test_reference_cull_counts_equal_twin(name, host_scene):
+    """CULL_REFERENCE visits exactly the boxes and triangles the reference's recursion visits"""
+    g = _util.load_golden(name)
+    hs = host_scene(name)
+    rays = _util.box_rays(g["root_box"], 4096, seed=1000)
+    want = _util.twin_bvh(hs).closest_hit(rays, counters=True)
+    got = _util.devsim_closest_hit(hs, rays, rtb.CULL_REFERENCE)
+    assert (got["box_tests"], got["tri_tests"]) == (want["box_tests"], want["tri_tests"])
+    glob = _util.devsim_closest_hit(hs, rays, rtb.CULL_GLOBAL)
+    assert glob["box_tests"] <= got["box_tests"] and glob["tri_tests"] <= got["tri_tests"]
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_light_pdf_bit_exact(name, host_scene):
+    g = _util.load_golden(name)
+    if "light_pdf" not in g.files:
+        pytest.skip("scene without emissive triangles")
+    assert np.array_equal(_util.devsim_light_pdf(host_scene(name), g["light_rays"]), g["light_pdf"])
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_paths_bit_exact(name, host_scene):
+    """Scene::intersect for explicit rays + engine seeds: same radiance bits, same engine state afterwards"""
+    g = _util.load_golden(name)
+    hs = host_scene(name)
+    rays = _util.camera_rays(_util.golden_camera(g), g["path_rgb"].shape[0], seed=4000)
+    bad = 0
+    for i in range(rays.shape[0]):
+        rgb, after = _util.devsim_trace_path(hs, rays[i, 0:3], rays[i, 3:6], 1 + i * 7919)
+        if after != int(g["path_engine_after"][i]) or not np.array_equal(rgb, g["path_rgb"][i]):
+            bad += 1
+    assert bad == 0
+
+
+@pytest.mark.parametrize("name", SCENES)
+@pytest.mark.parametrize("reference_cull", [False, True])
+def test_render_bit_exact(name, reference_cull, host_scene):
+    """the whole per-pixel loop (seeding, jitter, camera, bounce loop, accumulation, resolve) vs the reference's
+    deterministic render (per-pixel normal-distribution state, pixel 0 seeded with 1)"""
+    g = _util.load_golden(name)
+    hs = host_scene(name)
+    H, W, _ = g["render_accum"].shape
+    out = _util.devsim_render(hs, W, H, 4, pixel0_seed=1, reference_cull=reference_cull)
+    same = np.all(out["accum"] == g["render_accum"], axis=-1)
+    assert same.all(), "%d of %d pixels differ" % (np.count_nonzero(~same), same.size)
+    assert np.array_equal(out["rgb"], g["render_rgb"])
+    assert out["rays"] >= W * H * 4
+
+
+def test_libm_known_answers():
+    """glibc logf / powf / pow(x,5) restatements (csrc/rtb_libm.cuh) against the reference host's libm"""
+    import os
+    import subprocess
+    exe = os.path.join(_util.ROOT, "tests", "devsim", "libm_check")
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-C", os.path.dirname(exe), "libm_check"], check=True, stdout=subprocess.DEVNULL)
+    r = subprocess.run([exe, "1009"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout
