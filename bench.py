@@ -1,0 +1,337 @@
+#!/usr/bin/env python3
+"""bench.py -- the reference's headline workload on B200: the Sponza stand-in rendered by the sm_100a integrator.
+
+  python bench.py --gpus N --steps K --warmup W            (N>1: launched by torch.distributed.run, one rank per GPU)
+  python bench.py --impl reference ...                     (the reference's own OpenMP Scene::render on the host cores)
+
+A "step" is one full render of the workload (BASELINE.json configs[3]: examples/sponza at 1920x1080, 1024 spp --
+on the stand-in scene of scenes/gen_scenes.py, because the reference's geometry buffer was never shipped, SURVEY.md
+0.3).  Rows are dealt to the ranks in interleaved blocks (raytracing-hw_b200/dist.py); the step ends with the NCCL
+gather of the finished RGB8 rows on rank 0.  Total work is fixed as N grows: "scaling": "strong".
+
+value  : Mpix*spp/s of the whole job, scene resident in HBM, device-timed (CUDA events, max over ranks).
+e2e    : same metric through the C ABI with HOST buffers: rtb_scene_create (host->device copy of the whole scene) +
+         render + device->host copy of the image, every step.
+Prints ONE JSON line (rank 0)."""
+import argparse
+import importlib
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "scenes"))
+
+METRIC = "Sponza Mpix*spp/s (Mrays/s alongside) vs host-CPU OpenMP render"
+UNIT = "Mpix*spp/s"
+WORKLOADS = {
+    # name: (scene generator name, width, height, spp)
+    "sponza": ("sponza", 1920, 1080, 1024),      # BASELINE.json configs[3], the config the metric is quoted on
+    "s7_4": ("s7_4", 1280, 720, 256),            # configs[1]
+    "s6_1": ("s6_1", 320, 240, 16),              # configs[0]
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="sponza", choices=sorted(WORKLOADS))
+    ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (diagnostics only; 0 = the workload's)")
+    ap.add_argument("--width", type=int, default=0)
+    ap.add_argument("--height", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample", default="480x270x2", help="WxHxS of the bounded CPU sample")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = str(gpu_index)
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) >= 8 and f[0] == self.idx:
+                self.rows.append(f)
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+        sm = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        reasons = []
+        for k, name in ((4, "hw_slowdown"), (5, "hw_thermal_slowdown"), (6, "sw_thermal_slowdown"), (7, "sw_power_cap")):
+            if any(r[k].lower().startswith("active") for r in self.rows):
+                reasons.append(name)
+        mx = [float(r[2]) for r in self.rows if r[2].replace(".", "").isdigit()]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def workload(args):
+    scene, w, h, s = WORKLOADS[args.workload]
+    w, h, s = args.width or w, args.height or h, args.spp or s
+    name = "%s stand-in %dx%d %d spp" % (scene, w, h, s)
+    return scene, w, h, s, name
+
+
+# ------------------------------------------------------------------------------------------------ CPU side
+def cpu_reference_render(scene_path, w, h, s, threads=0):
+    """The reference's own Scene::render (OpenMP, as shipped) from oracle/_ref, timed around render() only.
+    Falls back to nothing: when oracle/_ref is absent the baseline is reported as unavailable."""
+    from oracle import ref_oracle
+    if not ref_oracle.available():
+        return None
+    rs = ref_oracle.RefScene.from_gltf(scene_path, w, h, s)
+    _, sec = rs.render(threads=threads)
+    rs.close()
+    return sec
+
+
+def cpu_baseline(scene_path, sample, rays_per_sample):
+    w, h, s = (int(x) for x in sample.split("x"))
+    cores = os.cpu_count() or 1
+    sec = cpu_reference_render(scene_path, w, h, s)
+    if sec is None:
+        return {"value": None, "unit": UNIT, "cores": cores, "kind": "reference", "sample": "oracle/_ref not present"}
+    v = w * h * s / sec * 1e-6
+    return {"value": v, "unit": UNIT, "cores": cores, "kind": "reference",
+            "sample": "%dx%d x %d spp of the same scene, Scene::render() only, OMP threads = %d, %.2f s" % (w, h, s, cores, sec),
+            "mrays_per_s": v * rays_per_sample if rays_per_sample else None}
+
+
+def run_reference_arm(args):
+    """--impl reference: the unmodified reference's CPU render of the workload, bounded sample per step, rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    import gen_scenes
+    scene, w, h, s, name = workload(args)
+    path = gen_scenes.ensure(scene)
+    cw, ch, cs = (int(x) for x in args.cpu_sample.split("x"))
+    cores = os.cpu_count() or 1
+    for _ in range(args.warmup):
+        cpu_reference_render(path, cw // 2, ch // 2, 1)
+    secs = []
+    for _ in range(args.steps):
+        sec = cpu_reference_render(path, cw, ch, cs)
+        if sec is None:
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libref_oracle.so is not present on this box"}))
+            return
+        secs.append(sec)
+    ms = statistics.mean(secs) * 1e3
+    v = cw * ch * cs / (ms * 1e-3) * 1e-6
+    sample = "%dx%d x %d spp of the %s scene per step, Scene::render() only, OMP threads = %d" % (cw, ch, cs, scene, cores)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic (stand-in scene, seeded generator)",
+        "config": {"workload": name, "sample_per_step": sample},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+# ------------------------------------------------------------------------------------------------ B200 arm
+def run_b200_arm(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import gen_scenes
+    rtb = importlib.import_module("raytracing-hw_b200")
+    rdist = importlib.import_module("raytracing-hw_b200.dist")
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if rtb.device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device: librtb.so has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    scene, W, H, S, name = workload(args)
+    if rank == 0:
+        path = gen_scenes.ensure(scene)       # deterministic generator; ranks > 0 wait for the files
+    barrier()
+    path = gen_scenes.ensure(scene)
+    hs = rtb.HostScene.load_gltf(path, W, H, S)
+    sc = rtb.Scene(hs, local)
+    params = rdist.rank_params(W, H, S, world, rank)
+    n_local = len(rdist.local_rows(params))
+    d_rgb = torch.empty((n_local, W, 3), dtype=torch.uint8, device="cuda")
+    d_cnt = torch.zeros(4, dtype=torch.int64, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
+    stream = torch.cuda.current_stream().cuda_stream
+    image = [None]
+
+    def step(ev=None):
+        if ev:
+            ev[0].record()
+        sc.render_device(params, d_accum=None, d_rgb8=d_rgb, d_counters=d_cnt, stream=stream)
+        if ev:
+            ev[1].record()
+        image[0] = rdist.gather_rows(d_rgb, W, H, S, world, rank)
+        if ev:
+            ev[2].record()
+
+    for _ in range(args.warmup):
+        flush.zero_()
+        step()
+    barrier()
+    d_cnt.zero_()
+    sampler = ClockSampler(local)
+    sampler.start()
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    barrier()
+    t_wall = time.perf_counter()
+    for k in range(args.steps):
+        flush.zero_()
+        step(evs[k])
+    barrier()
+    t_wall = time.perf_counter() - t_wall
+    clocks = sampler.stop()
+    step_ms = sum(e[0].elapsed_time(e[2]) for e in evs)
+    kern_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
+    t = torch.tensor([step_ms], dtype=torch.float64, device="cuda")
+    cnt = d_cnt.clone()
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    ms_per_step = float(t[0]) / args.steps
+    rays_per_step = int(cnt[0]) / args.steps
+    lq_per_step = int(cnt[1]) / args.steps
+    value = W * H * S / (ms_per_step * 1e-3) * 1e-6
+
+    # ---- e2e: host buffers through the C ABI; scene upload + render + image download inside the timed region
+    h_rgb = torch.empty((n_local, W, 3), dtype=torch.uint8).pin_memory()
+    h_img = torch.empty((H, W, 3), dtype=torch.uint8).pin_memory() if rank == 0 else None
+    upload_bytes = sc.upload_bytes
+
+    def e2e_step():
+        s2 = rtb.Scene(hs, local)                                   # H2D: nodes, triangles, shading records, textures
+        if world == 1:
+            s2.render(W, H, S, params=params, want_accum=False, rgb=h_rgb.numpy())      # D2H inside rtb_render
+        else:
+            s2.render_device(params, d_accum=None, d_rgb8=d_rgb, d_counters=None, stream=stream)
+            img = rdist.gather_rows(d_rgb, W, H, S, world, rank)
+            if rank == 0:
+                h_img.copy_(img, non_blocking=True)
+            torch.cuda.synchronize()
+        s2.close()
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    n_e2e = max(1, min(args.steps, 2))
+    for _ in range(n_e2e):
+        e2e_step()
+    barrier()
+    te = torch.tensor([(time.perf_counter() - t0) / n_e2e], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = W * H * S / float(te[0]) * 1e-6
+    return dict(rtb=rtb, sc=sc, hs=hs, path=path, rank=rank, world=world, W=W, H=H, S=S, name=name, value=value,
+                ms_per_step=ms_per_step, kern_ms=kern_ms, rays_per_step=rays_per_step, lq_per_step=lq_per_step,
+                clocks=clocks, e2e_value=e2e_value, upload_bytes=upload_bytes, t_wall=t_wall, params=params,
+                n_local=n_local, torch=torch, dist=dist)
+
+
+def roofline(r):
+    """dominant kernel = k_render.  Algorithmic bytes = 28 B per ray/box test + 36 B per ray/triangle test
+     performed by the shipped traversal order, counted by the counting instantiation of the same kernel
+    at a reduced spp on the same rows and scaled by the sample ratio (tests per sample are spp-independent)."""
+    rtb, sc, p = r["rtb"], r["sc"], r["params"]
+    spp_c = min(r["S"], 4)
+    pc = rtb.RenderParams(p.width, p.height, spp_c, p.row_begin, p.row_end, p.pixel0_seed, 0, 1, p.interleave_count,
+                          p.interleave_index, p.interleave_rows)
+    st = sc.render(p.width, p.height, spp_c, params=pc, want_accum=False, want_rgb=False)["stats"]
+    scale = r["S"] / spp_c
+    box, tri = st["box_tests"] * scale, st["tri_tests"] * scale
+    bytes_launch = 28.0 * box + 36.0 * tri
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    else:
+        peak, src = 6650.0, "fallback 6.65 TB/s (of fallback)"
+    achieved = bytes_launch / (r["kern_ms"] * 1e-3) * 1e-9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        t = json.load(open(tpath)).get(r["name"])
+        traffic = t.get("dram_bytes_per_launch") if t else None
+    n_samples = r["n_local"] * r["W"] * r["S"]
+    return {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+            "kernel": "k_render", "kernel_ms": r["kern_ms"], "algorithmic_bytes_per_launch": bytes_launch, "peak_source": src,
+            "box_tests_per_ray": box / max(1.0, st["closest_hit_rays"] * scale), "tri_tests_per_ray": tri / max(1.0, st["closest_hit_rays"] * scale),
+            "bytes_per_sample": bytes_launch / max(1, n_samples),
+            "note": "scene traversal set (%.1f MB) is L2-resident: the HBM peak is the contract's denominator, not the binding limit; "
+                    "see DESIGN.md" % (sc.traversal_bytes / 1e6)}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+    r = run_b200_arm(args)
+    roof = roofline(r)
+    if r["world"] > 1:
+        r["dist"].barrier()
+    if r["rank"] == 0:
+        rays_per_sample = r["rays_per_step"] / (r["W"] * r["H"] * r["S"])
+        line = {
+            "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": r["world"], "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic (stand-in scene from the seeded generator scenes/gen_scenes.py; the reference's geometry buffers were never shipped)",
+            "config": {"workload": r["name"], "parallelism": "row-block interleave x%d, NCCL all_gather of RGB8 rows" % r["world"],
+                       "l2": "256 MB buffer written between timed steps (L2 flush)", "ray_depth": 6},
+            "mrays_per_s": r["rays_per_step"] / (r["ms_per_step"] * 1e-3) * 1e-6,
+            "light_pdf_mqueries_per_s": r["lq_per_step"] / (r["ms_per_step"] * 1e-3) * 1e-6,
+            "rays_per_sample": rays_per_sample,
+            "clocks": r["clocks"],
+            "e2e": {"value": r["e2e_value"], "unit": UNIT, "h2d_bytes_per_step": int(r["upload_bytes"]) * r["world"],
+                    "d2h_bytes_per_step": r["W"] * r["H"] * 3},
+            "gpu_launches": args.steps * r["world"],
+            "roofline": roof,
+        }
+        if r["world"] == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(r["path"], args.cpu_sample, rays_per_sample)
+        print(json.dumps(line))
+    if r["world"] > 1:
+        r["dist"].barrier()
+        r["dist"].destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

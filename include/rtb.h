@@ -154,6 +154,8 @@ void rtb_scene_destroy(rtb_scene *scene);
 int rtb_scene_device(const rtb_scene *scene);
 /* bytes of device memory holding nodes+triangles (the traversal working set) */
 size_t rtb_scene_traversal_bytes(const rtb_scene *scene);
+/* host->device bytes rtb_scene_create copied for this scene (nodes, triangles, shading records, textures, ...) */
+size_t rtb_scene_upload_bytes(const rtb_scene *scene);
 
 /* Replaces BVH::intersect (src/core/bvh.cpp:239-243) for a batch.  rays6: n x 6 floats = origin xyz, direction xyz
  * (un-normalised; normalised on device exactly as Ray::Ray does, src/geometry/primitive.cpp:12-15).

@@ -23,7 +23,7 @@ ABI_SYMBOLS = [
     "rtb_last_error", "rtb_device_count",
     "rtb_host_scene_load_gltf", "rtb_host_scene_from_triangles", "rtb_host_scene_desc", "rtb_host_scene_bvh_stats",
     "rtb_host_scene_build_seconds", "rtb_host_scene_destroy",
-    "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_device", "rtb_scene_traversal_bytes",
+    "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_device", "rtb_scene_traversal_bytes", "rtb_scene_upload_bytes",
     "rtb_closest_hit", "rtb_closest_hit_device", "rtb_light_pdf",
     "rtb_render", "rtb_render_device", "rtb_resolve_device", "rtb_render_local_rows", "rtb_render_global_row",
     "rtb_write_ppm",
@@ -84,6 +84,8 @@ def lib():
         L.rtb_host_scene_build_seconds.argtypes = [C.c_void_p]
         L.rtb_scene_traversal_bytes.restype = C.c_size_t
         L.rtb_scene_traversal_bytes.argtypes = [C.c_void_p]
+        L.rtb_scene_upload_bytes.restype = C.c_size_t
+        L.rtb_scene_upload_bytes.argtypes = [C.c_void_p]
         L.rtb_host_scene_load_gltf.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
         L.rtb_host_scene_from_triangles.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p, C.c_void_p,
                                                     C.c_float, C.c_float, C.c_float, C.POINTER(C.c_void_p)]
@@ -241,6 +243,10 @@ class Scene:
     @property
     def traversal_bytes(self):
         return lib().rtb_scene_traversal_bytes(self.h)
+
+    @property
+    def upload_bytes(self):
+        return lib().rtb_scene_upload_bytes(self.h)
 
     def closest_hit(self, rays, cull=CULL_GLOBAL, counters=False, out=None):
         """rays: (n,6) float32 host array (numpy or pinned torch).  Returns dict(id,t,u,v,inside,stats)."""

@@ -29,6 +29,7 @@ struct rtb_scene {
     rtb::DScene d;
     std::vector<void *> allocs;
     size_t traversal_bytes = 0;
+    size_t upload_bytes = 0;   // host->device bytes copied by rtb_scene_create
     cudaStream_t streams[3] = {nullptr, nullptr, nullptr};
     cudaEvent_t ev[2] = {nullptr, nullptr};
     // staging buffers reused across calls
@@ -55,6 +56,7 @@ int upload(rtb_scene *sc, const std::vector<T> &h, const T **out) {
     RTB_CUDA(cudaMalloc(&p, h.size() * sizeof(T)));
     sc->allocs.push_back(p);
     RTB_CUDA(cudaMemcpy(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+    sc->upload_bytes += h.size() * sizeof(T);
     *out = (const T *) p;
     return RTB_OK;
 }
@@ -131,6 +133,7 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
             RTB_CUDA(cudaMalloc(&p, bytes));
             sc->allocs.push_back(p);
             RTB_CUDA(cudaMemcpy(p, t.rgba, bytes, cudaMemcpyHostToDevice));
+            sc->upload_bytes += bytes;
             tex[i] = {(const uchar4 *) p, t.width, t.height};
         }
         if ((rc = upload(sc, tex, &sc->d.textures)) != RTB_OK) return fail(rc);
@@ -146,6 +149,7 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
 void rtb_scene_destroy(rtb_scene *scene) { delete scene; }
 int rtb_scene_device(const rtb_scene *scene) { return scene ? scene->device : -1; }
 size_t rtb_scene_traversal_bytes(const rtb_scene *scene) { return scene ? scene->traversal_bytes : 0; }
+size_t rtb_scene_upload_bytes(const rtb_scene *scene) { return scene ? scene->upload_bytes : 0; }
 
 int rtb_closest_hit_device(rtb_scene *scene, const float *d_rays6, size_t n, int cull_mode, int32_t *d_id, float *d_t, float *d_u,
                            float *d_v, uint8_t *d_inside, unsigned long long *d_counters, void *stream) {
