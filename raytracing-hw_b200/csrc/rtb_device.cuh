@@ -227,7 +227,7 @@ struct Counters {
 // BVH::intersect (bvh.cpp:239-243).  CULL = 0: the reference's sibling-only culling, reproduced exactly with a
 // "min since push" value per deferred sibling; CULL = 1: global-best culling (same visit order, subset of visits).
 template <int CULL, bool COUNT>
-RTB_HD bool closest_hit(const DBvh &b, const Ray &r, Hit &best, Counters *cnt) {
+RTB_HD bool closest_hit_ordered(const DBvh &b, const Ray &r, Hit &best, Counters *cnt) {
     best.t = kFar;
     best.id = -1;
     best.u = 0.f;

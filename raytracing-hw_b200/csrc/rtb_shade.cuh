@@ -15,6 +15,7 @@
 #pragma once
 #include "rtb_device.cuh"
 #include "rtb_libm.cuh"
+#include "rtb_traverse.cuh"
 
 namespace rtb {
 
