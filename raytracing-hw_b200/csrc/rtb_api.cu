@@ -24,12 +24,16 @@ void set_error(const std::string &e);
         }                                                                                                           \
     } while (0)
 
+constexpr unsigned kQueueHeads = 64;
+
 struct rtb_scene {
     int device = 0;
     rtb::DScene d;
     std::vector<void *> allocs;
     size_t traversal_bytes = 0;
-    size_t upload_bytes = 0;   // host->device bytes copied by rtb_scene_create
+    size_t upload_bytes = 0;
+    unsigned *queue_heads = nullptr;   // kQueueHeads ray-queue cursors, rotated per launch (stream-ordered memset)
+    unsigned next_head = 0;   // host->device bytes copied by rtb_scene_create
     cudaStream_t streams[3] = {nullptr, nullptr, nullptr};
     cudaEvent_t ev[2] = {nullptr, nullptr};
     // staging buffers reused across calls
@@ -39,6 +43,7 @@ struct rtb_scene {
         cudaSetDevice(device);
         for (void *p : allocs) cudaFree(p);
         if (stage) cudaFree(stage);
+        if (queue_heads) cudaFree(queue_heads);
         for (auto &s : streams) if (s) cudaStreamDestroy(s);
         for (auto &e : ev) if (e) cudaEventDestroy(e);
     }
@@ -140,6 +145,7 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
     }
     fill_scalars(desc, sc->d);
 
+    RTB_CUDA(cudaMalloc((void **) &sc->queue_heads, kQueueHeads * sizeof(unsigned)));
     for (auto &s : sc->streams) RTB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
     for (auto &e : sc->ev) RTB_CUDA(cudaEventCreate(&e));
     *out = sc;
@@ -156,7 +162,8 @@ int rtb_closest_hit_device(rtb_scene *scene, const float *d_rays6, size_t n, int
     if (!scene || !d_rays6 || !d_id) { rtb::set_error("rtb_closest_hit_device: null argument"); return RTB_ERR_INVALID; }
     if (cull_mode != RTB_CULL_REFERENCE && cull_mode != RTB_CULL_GLOBAL) { rtb::set_error("rtb_closest_hit_device: bad cull mode"); return RTB_ERR_INVALID; }
     RTB_CUDA(cudaSetDevice(scene->device));
-    rtb::launch_closest_hit(scene->d, d_rays6, n, cull_mode, d_id, d_t, d_u, d_v, d_inside, d_counters, (cudaStream_t) stream);
+    rtb::launch_closest_hit(scene->d, d_rays6, n, cull_mode, d_id, d_t, d_u, d_v, d_inside, d_counters,
+                            scene->queue_heads + (scene->next_head++ % kQueueHeads), (cudaStream_t) stream);
     RTB_CUDA(cudaGetLastError());
     return RTB_OK;
 }
@@ -197,7 +204,7 @@ int rtb_closest_hit(rtb_scene *scene, const float *rays6, size_t n, int cull_mod
         uint8_t *d_in = (uint8_t *) (base + chunk * 40);
         RTB_CUDA(cudaMemcpyAsync(d_rays, rays6 + off * 6, m * 24, cudaMemcpyHostToDevice, st));
         rtb::launch_closest_hit(scene->d, d_rays, m, cull_mode, d_id, t ? d_t : nullptr, u ? d_u : nullptr, v ? d_v : nullptr,
-                                inside ? d_in : nullptr, d_cnt, st);
+                                inside ? d_in : nullptr, d_cnt, scene->queue_heads + (scene->next_head++ % kQueueHeads), st);
         ++launches;
         RTB_CUDA(cudaMemcpyAsync(id + off, d_id, m * 4, cudaMemcpyDeviceToHost, st));
         if (t) RTB_CUDA(cudaMemcpyAsync(t + off, d_t, m * 4, cudaMemcpyDeviceToHost, st));

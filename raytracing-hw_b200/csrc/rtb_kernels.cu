@@ -2,7 +2,9 @@
 // memory, node = 4 x LDG.128, triangle = 3 x LDG.128 through the read-only path.
 // Compiled with --fmad=false (decision-exact float arithmetic, see rtb_device.cuh).
 #include "rtb_kernels.cuh"
+#include <algorithm>
 #include "rtb_shade.cuh"
+#include "rtb_trace.cuh"
 
 namespace rtb {
 
@@ -51,10 +53,74 @@ __global__ void __launch_bounds__(128) k_closest_hit(const __grid_constant__ DSc
     }
 }
 
+// Persistent ray-queue variant (RTB_CULL_GLOBAL): see rtb_trace.cuh.  grid = a few CTAs per SM; lanes pull rays.
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_closest_hit_queue(const __grid_constant__ DScene sc, const float *__restrict__ rays6, unsigned n,
+                                                           unsigned *__restrict__ queue_head, int *__restrict__ id,
+                                                           float *__restrict__ t, float *__restrict__ u, float *__restrict__ v,
+                                                           uint8_t *__restrict__ inside, unsigned long long *__restrict__ counters) {
+    Counters cnt = {0ull, 0ull};
+    trace_persistent<COUNT>(
+        sc.bvh, n, queue_head,
+        [&](unsigned i, Ray &r) {
+            const float2 *rp = reinterpret_cast<const float2 *>(rays6 + (size_t) i * 6);
+            const float2 r0 = __ldg(rp), r1 = __ldg(rp + 1), r2 = __ldg(rp + 2);
+            make_ray(r, r0.x, r0.y, r1.x, r1.y, r2.x, r2.y);
+        },
+        [&](unsigned i, const Ray &r, const Hit &h) {
+            const bool ok = h.id >= 0;
+            id[i] = ok ? h.id : -1;
+            if (t) t[i] = ok ? h.t : 0.f;
+            if (u) u[i] = ok ? h.u : 0.f;
+            if (v) v[i] = ok ? h.v : 0.f;
+            if (inside) {
+                uint8_t in = 0;
+                if (ok) {   // `if (dot(ray.direction, normal) > 0) inside = true` (primitive.cpp:51-54)
+                    const float4 q2 = __ldg(sc.bvh.tris + (size_t) h.id * 3 + 2);
+                    float dn = r.d[0] * q2.y;
+                    dn = dn + r.d[1] * q2.z;
+                    dn = dn + r.d[2] * q2.w;
+                    in = dn > 0.f ? 1 : 0;
+                }
+                inside[i] = in;
+            }
+        },
+        &cnt);
+    if (COUNT) {
+        for (int o = 16; o > 0; o >>= 1) {
+            cnt.box += __shfl_down_sync(0xffffffffu, cnt.box, o);
+            cnt.tri += __shfl_down_sync(0xffffffffu, cnt.tri, o);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(&counters[0], cnt.box);
+            atomicAdd(&counters[1], cnt.tri);
+        }
+    }
+}
+
+int persistent_grid(int threads_per_block, int blocks_per_sm) {
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (sms <= 0) sms = 148;
+    }
+    (void) threads_per_block;
+    return sms * blocks_per_sm;
+}
+
 void launch_closest_hit(const DScene &sc, const float *d_rays6, size_t n, int cull_mode, int *d_id, float *d_t, float *d_u,
-                        float *d_v, uint8_t *d_inside, unsigned long long *d_counters, cudaStream_t stream) {
+                        float *d_v, uint8_t *d_inside, unsigned long long *d_counters, unsigned *d_queue_head, cudaStream_t stream) {
     if (n == 0) return;
     const unsigned block = 128;
+    if (cull_mode == 1 && d_queue_head != nullptr && n < 0xFFFFFF00u) {
+        cudaMemsetAsync(d_queue_head, 0, sizeof(unsigned), stream);
+        const unsigned pg = (unsigned) std::min<size_t>((n + block - 1) / block, (size_t) persistent_grid(block, 8));
+        if (d_counters) k_closest_hit_queue<true><<<pg, block, 0, stream>>>(sc, d_rays6, (unsigned) n, d_queue_head, d_id, d_t, d_u, d_v, d_inside, d_counters);
+        else k_closest_hit_queue<false><<<pg, block, 0, stream>>>(sc, d_rays6, (unsigned) n, d_queue_head, d_id, d_t, d_u, d_v, d_inside, d_counters);
+        return;
+    }
     const unsigned grid = (unsigned) ((n + block - 1) / block);
     const bool count = d_counters != nullptr;
     if (cull_mode == 0) {

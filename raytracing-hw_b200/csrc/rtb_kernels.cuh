@@ -5,7 +5,8 @@
 namespace rtb {
 
 void launch_closest_hit(const DScene &sc, const float *d_rays6, size_t n, int cull_mode, int *d_id, float *d_t, float *d_u,
-                        float *d_v, uint8_t *d_inside, unsigned long long *d_counters, cudaStream_t stream);
+                        float *d_v, uint8_t *d_inside, unsigned long long *d_counters, unsigned *d_queue_head, cudaStream_t stream);
+int persistent_grid(int threads_per_block, int blocks_per_sm);
 
 void launch_light_pdf(const DScene &sc, const float *d_rays6, size_t n, float *d_pdf, cudaStream_t stream);
 

@@ -1,0 +1,5 @@
+mkdir -p gpurun_out
+C="python tools/bench_closest_hit.py --rays 4000000 --reps 1"
+$C > gpurun_out/prof_plain_ch.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:k_closest_hit_queue -s 2 -c 1 -o gpurun_out/r01c_k_closest_hit_queue $C > gpurun_out/ncu_ch.log 2>&1
+tail -3 gpurun_out/ncu_ch.log
