@@ -48,7 +48,8 @@ def parse_args():
     ap.add_argument("--width", type=int, default=0)
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-sample", default="480x270x2", help="WxHxS of the bounded CPU sample")
+    ap.add_argument("--cpu-sample", default="960x540x24", help="WxHxS of the bounded CPU sample (about 10-30 s of host work)")
+    ap.add_argument("--megakernel", action="store_true", help="time the first integrator (one thread per pixel) instead of the ray queue")
     return ap.parse_args()
 
 
@@ -190,7 +191,9 @@ def run_b200_arm(args):
     params = rdist.rank_params(W, H, S, world, rank)
     n_local = len(rdist.local_rows(params))
     d_rgb = torch.empty((n_local, W, 3), dtype=torch.uint8, device="cuda")
-    d_cnt = torch.zeros(4, dtype=torch.int64, device="cuda")
+    d_cnt = torch.zeros(6, dtype=torch.int64, device="cuda")
+    if args.megakernel:
+        params.flags |= rtb.RENDER_MEGAKERNEL
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
     stream = torch.cuda.current_stream().cuda_stream
     image = [None]
@@ -212,6 +215,7 @@ def run_b200_arm(args):
     d_cnt.zero_()
     sampler = ClockSampler(local)
     sampler.start()
+    launches0 = sc.launches
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
     barrier()
     t_wall = time.perf_counter()
@@ -221,6 +225,7 @@ def run_b200_arm(args):
     barrier()
     t_wall = time.perf_counter() - t_wall
     clocks = sampler.stop()
+    launches = sc.launches - launches0
     step_ms = sum(e[0].elapsed_time(e[2]) for e in evs)
     kern_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
     t = torch.tensor([step_ms], dtype=torch.float64, device="cuda")
@@ -264,37 +269,52 @@ def run_b200_arm(args):
     return dict(rtb=rtb, sc=sc, hs=hs, path=path, rank=rank, world=world, W=W, H=H, S=S, name=name, value=value,
                 ms_per_step=ms_per_step, kern_ms=kern_ms, rays_per_step=rays_per_step, lq_per_step=lq_per_step,
                 clocks=clocks, e2e_value=e2e_value, upload_bytes=upload_bytes, t_wall=t_wall, params=params,
-                n_local=n_local, torch=torch, dist=dist)
+                n_local=n_local, torch=torch, dist=dist, launches=launches, d_rgb=d_rgb, stream=stream, megakernel=args.megakernel)
 
 
 def roofline(r):
-    """dominant kernel = k_render.  Algorithmic bytes = 28 B per ray/box test + 36 B per ray/triangle test
-     performed by the shipped traversal order, counted by the counting instantiation of the same kernel
-    at a reduced spp on the same rows and scaled by the sample ratio (tests per sample are spp-independent)."""
+    """Dominant kernel: k_wf_trace, the closest-hit queue (k_render with --megakernel).  Algorithmic bytes = 28 B per
+    ray/box test + 36 B per ray/triangle test performed by the shipped traversal order on the scene BVH,
+    counted by the counting instantiation of the same kernels at a reduced spp on the same rows and scaled by the
+    sample ratio (tests per sample are spp-independent).  Kernel time: CUDA events recorded on the launching stream
+    around every queue launch of one extra frame (RTB_RENDER_STAGE_TIMES); `achieved` = all queue launches' bytes /
+    all queue launches' time = bytes per launch / average launch duration."""
     rtb, sc, p = r["rtb"], r["sc"], r["params"]
     spp_c = min(r["S"], 4)
-    pc = rtb.RenderParams(p.width, p.height, spp_c, p.row_begin, p.row_end, p.pixel0_seed, 0, 1, p.interleave_count,
-                          p.interleave_index, p.interleave_rows)
+    pc = rtb.RenderParams(p.width, p.height, spp_c, p.row_begin, p.row_end, p.pixel0_seed, 0, 1 | (p.flags & rtb.RENDER_MEGAKERNEL),
+                          p.interleave_count, p.interleave_index, p.interleave_rows)
     st = sc.render(p.width, p.height, spp_c, params=pc, want_accum=False, want_rgb=False)["stats"]
     scale = r["S"] / spp_c
-    box, tri = st["box_tests"] * scale, st["tri_tests"] * scale
-    bytes_launch = 28.0 * box + 36.0 * tri
+    if r["megakernel"]:
+        box, tri = st["box_tests"] * scale, st["tri_tests"] * scale
+        kernel, kernel_ms, n_launch, other_ms = "k_render", r["kern_ms"], 1, 0.0
+    else:
+        box, tri = (st["box_tests"] - st["light_box_tests"]) * scale, (st["tri_tests"] - st["light_tri_tests"]) * scale
+        pt = rtb.RenderParams(p.width, p.height, p.samples, p.row_begin, p.row_end, p.pixel0_seed, 0, rtb.RENDER_STAGE_TIMES,
+                              p.interleave_count, p.interleave_index, p.interleave_rows)
+        sc.render_device(pt, d_accum=None, d_rgb8=r["d_rgb"], d_counters=None, stream=r["stream"])
+        kernel_ms, other_ms, n_launch = sc.stage_ms()
+        kernel = "k_wf_trace"
+    bytes_all = 28.0 * box + 36.0 * tri
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         peak, src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
     else:
         peak, src = 6650.0, "fallback 6.65 TB/s (of fallback)"
-    achieved = bytes_launch / (r["kern_ms"] * 1e-3) * 1e-9
+    achieved = bytes_all / (kernel_ms * 1e-3) * 1e-9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         t = json.load(open(tpath)).get(r["name"])
         traffic = t.get("dram_bytes_per_launch") if t else None
     n_samples = r["n_local"] * r["W"] * r["S"]
+    rays = max(1.0, st["closest_hit_rays"] * scale)
     return {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-            "kernel": "k_render", "kernel_ms": r["kern_ms"], "algorithmic_bytes_per_launch": bytes_launch, "peak_source": src,
-            "box_tests_per_ray": box / max(1.0, st["closest_hit_rays"] * scale), "tri_tests_per_ray": tri / max(1.0, st["closest_hit_rays"] * scale),
-            "bytes_per_sample": bytes_launch / max(1, n_samples),
+            "kernel": kernel, "kernel_launches": int(n_launch), "kernel_ms_total": kernel_ms, "kernel_ms_avg": kernel_ms / max(1, n_launch),
+            "kernel_share_of_step": kernel_ms / max(1e-9, kernel_ms + other_ms), "other_kernels_ms_total": other_ms,
+            "algorithmic_bytes_per_launch": bytes_all / max(1, n_launch), "peak_source": src,
+            "box_tests_per_ray": box / rays, "tri_tests_per_ray": tri / rays, "kernel_mrays_per_s": rays / (kernel_ms * 1e-3) * 1e-6,
+            "bytes_per_sample": bytes_all / max(1, n_samples),
             "note": "scene traversal set (%.1f MB) is L2-resident: the HBM peak is the contract's denominator, not the binding limit; "
                     "see DESIGN.md" % (sc.traversal_bytes / 1e6)}
 
@@ -322,7 +342,7 @@ def main():
             "clocks": r["clocks"],
             "e2e": {"value": r["e2e_value"], "unit": UNIT, "h2d_bytes_per_step": int(r["upload_bytes"]) * r["world"],
                     "d2h_bytes_per_step": r["W"] * r["H"] * 3},
-            "gpu_launches": args.steps * r["world"],
+            "gpu_launches": int(r["launches"]) * r["world"],
             "roofline": roof,
         }
         if r["world"] == 1 and not args.no_cpu_baseline:

@@ -109,7 +109,12 @@ int rtb_render_global_row(const rtb_render_params *params, int local_row);
 
 #define RTB_RENDER_COUNTERS 1        /* also count box / triangle tests (slower instantiation of the kernel); rays and
                                         light queries are always counted                                                */
-#define RTB_RENDER_REFERENCE_CULL 2  /* traverse with RTB_CULL_REFERENCE instead of the default RTB_CULL_GLOBAL          */
+#define RTB_RENDER_REFERENCE_CULL 2  /* traverse with RTB_CULL_REFERENCE instead of the default RTB_CULL_GLOBAL
+                                        (implies the megakernel integrator)                                              */
+#define RTB_RENDER_STAGE_TIMES 8     /* record CUDA events around every closest-hit queue launch (rtb_scene_stage_ms)   */
+#define RTB_RENDER_MEGAKERNEL 4      /* one thread per pixel runs the whole bounce loop (the first integrator; kept for
+                                        A/B measurements).  Default: the wavefront / ray-queue integrator, whose sums
+                                        are bit-identical to the megakernel's                                            */
 
 /* set rtb_stats.box_tests to this value before a call to ask for box/triangle test counts (a slower, counting
  * instantiation of the kernel is launched); otherwise box_tests / tri_tests come back 0.                          */
@@ -123,6 +128,8 @@ typedef struct rtb_stats {
     double kernel_ms;             /* device time of the render / closest-hit kernels of this call (CUDA events)       */
     double h2d_ms, d2h_ms;        /* copies inside this call                                                          */
     uint64_t launches;            /* kernels launched by this call                                                    */
+    uint64_t light_box_tests;     /* the part of box_tests / tri_tests done by the light-pdf queries (light BVH)      */
+    uint64_t light_tri_tests;
 } rtb_stats;
 
 const char *rtb_last_error(void);
@@ -156,6 +163,12 @@ int rtb_scene_device(const rtb_scene *scene);
 size_t rtb_scene_traversal_bytes(const rtb_scene *scene);
 /* host->device bytes rtb_scene_create copied for this scene (nodes, triangles, shading records, textures, ...) */
 size_t rtb_scene_upload_bytes(const rtb_scene *scene);
+/* kernels launched so far by rtb_render / rtb_render_device calls on this scene */
+unsigned long long rtb_scene_launches(const rtb_scene *scene);
+/* After a render with RTB_RENDER_STAGE_TIMES (wavefront integrator): waits for the frame and returns the summed
+ * device time (CUDA events on the launching stream) of the closest-hit queue kernel launches, of everything else
+ * in the frame (shade + compaction), and the number of queue launches.                                           */
+int rtb_scene_stage_ms(rtb_scene *scene, double *trace_ms, double *other_ms, unsigned long long *trace_launches);
 
 /* Replaces BVH::intersect (src/core/bvh.cpp:239-243) for a batch.  rays6: n x 6 floats = origin xyz, direction xyz
  * (un-normalised; normalised on device exactly as Ray::Ray does, src/geometry/primitive.cpp:12-15).
@@ -177,7 +190,8 @@ int rtb_light_pdf(rtb_scene *scene, const float *rays6, size_t n, float *pdf);
  * rgb8  (may be NULL): (row_end-row_begin) x width x 3 bytes after x(1/samples), ACES, gamma 1/2.2, round.
  * HOST pointers; the device->host copy is inside the call.                                                         */
 int rtb_render(rtb_scene *scene, const rtb_render_params *params, float *accum, uint8_t *rgb8, rtb_stats *stats);
-/* same, DEVICE output pointers, asynchronous on `stream`; d_counters: 4 uint64 {rays, light queries, box, tri} or NULL */
+/* same, DEVICE output pointers, asynchronous on `stream`; d_counters: 6 uint64 {rays, light queries, box, tri,
+ * light-query box, light-query tri} or NULL (box / tri are totals over both BVHs and need RTB_RENDER_COUNTERS)    */
 int rtb_render_device(rtb_scene *scene, const rtb_render_params *params, float *d_accum, uint8_t *d_rgb8,
                       unsigned long long *d_counters, void *stream);
 /* resolve only (src/core/scene.cpp:54-63): d_accum (n_pixels x 3 sums) -> d_rgb8 */

@@ -16,6 +16,7 @@ LIB_PATH = os.path.join(_HERE, "librtb.so")
 
 RTB_OK, RTB_ERR_INVALID, RTB_ERR_NO_DEVICE, RTB_ERR_CUDA, RTB_ERR_IO = 0, 1, 2, 3, 4
 CULL_REFERENCE, CULL_GLOBAL = 0, 1
+RENDER_COUNTERS, RENDER_REFERENCE_CULL, RENDER_MEGAKERNEL, RENDER_STAGE_TIMES = 1, 2, 4, 8
 REQUEST_COUNTERS = 0xFFFFFFFFFFFFFFFF
 
 # every symbol include/rtb.h declares (tests/test_abi.py checks the library exports all of them)
@@ -23,7 +24,7 @@ ABI_SYMBOLS = [
     "rtb_last_error", "rtb_device_count",
     "rtb_host_scene_load_gltf", "rtb_host_scene_from_triangles", "rtb_host_scene_desc", "rtb_host_scene_bvh_stats",
     "rtb_host_scene_build_seconds", "rtb_host_scene_destroy",
-    "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_device", "rtb_scene_traversal_bytes", "rtb_scene_upload_bytes",
+    "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_device", "rtb_scene_traversal_bytes", "rtb_scene_upload_bytes", "rtb_scene_launches", "rtb_scene_stage_ms",
     "rtb_closest_hit", "rtb_closest_hit_device", "rtb_light_pdf",
     "rtb_render", "rtb_render_device", "rtb_resolve_device", "rtb_render_local_rows", "rtb_render_global_row",
     "rtb_write_ppm",
@@ -57,7 +58,7 @@ class RenderParams(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("closest_hit_rays", C.c_uint64), ("light_pdf_queries", C.c_uint64), ("box_tests", C.c_uint64),
                 ("tri_tests", C.c_uint64), ("kernel_ms", C.c_double), ("h2d_ms", C.c_double), ("d2h_ms", C.c_double),
-                ("launches", C.c_uint64)]
+                ("launches", C.c_uint64), ("light_box_tests", C.c_uint64), ("light_tri_tests", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -86,6 +87,9 @@ def lib():
         L.rtb_scene_traversal_bytes.argtypes = [C.c_void_p]
         L.rtb_scene_upload_bytes.restype = C.c_size_t
         L.rtb_scene_upload_bytes.argtypes = [C.c_void_p]
+        L.rtb_scene_launches.restype = C.c_ulonglong
+        L.rtb_scene_launches.argtypes = [C.c_void_p]
+        L.rtb_scene_stage_ms.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_ulonglong)]
         L.rtb_host_scene_load_gltf.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
         L.rtb_host_scene_from_triangles.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p, C.c_void_p,
                                                     C.c_float, C.c_float, C.c_float, C.POINTER(C.c_void_p)]
@@ -248,6 +252,16 @@ class Scene:
     def upload_bytes(self):
         return lib().rtb_scene_upload_bytes(self.h)
 
+    @property
+    def launches(self):
+        return lib().rtb_scene_launches(self.h)
+
+    def stage_ms(self):
+        """(queue-kernel ms, everything-else ms, queue launches) of the last render with RENDER_STAGE_TIMES"""
+        a, b, n = C.c_double(), C.c_double(), C.c_ulonglong()
+        _check(lib().rtb_scene_stage_ms(self.h, C.byref(a), C.byref(b), C.byref(n)))
+        return a.value, b.value, n.value
+
     def closest_hit(self, rays, cull=CULL_GLOBAL, counters=False, out=None):
         """rays: (n,6) float32 host array (numpy or pinned torch).  Returns dict(id,t,u,v,inside,stats)."""
         n = rays.shape[0]
@@ -274,11 +288,11 @@ class Scene:
         return out
 
     def render(self, width, height, samples, rows=None, pixel0_seed=1, counters=False, want_accum=True, want_rgb=True,
-               accum=None, rgb=None, reference_cull=False, params=None):
+               accum=None, rgb=None, reference_cull=False, megakernel=False, params=None):
         """Replaces Scene::render.  HOST output buffers (numpy or pinned torch); copies are inside the call."""
         if params is None:
             r0, r1 = rows if rows is not None else (0, height)
-            flags = (1 if counters else 0) | (2 if reference_cull else 0)
+            flags = (1 if counters else 0) | (2 if reference_cull else 0) | (4 if megakernel else 0)
             params = RenderParams(width, height, samples, r0, r1, pixel0_seed, 0, flags)
         n = lib().rtb_render_local_rows(C.byref(params))
         if n < 0:

@@ -39,10 +39,18 @@ struct rtb_scene {
     // staging buffers reused across calls
     void *stage = nullptr;
     size_t stage_bytes = 0;
+    // path state of the wavefront integrator (rtb_wavefront.cuh), grown on demand
+    void *wf_state = nullptr;
+    size_t wf_bytes = 0;
+    unsigned long long launches = 0;   // kernels launched by rtb_render_device calls on this scene
+    std::vector<cudaEvent_t> stage_events;   // RTB_RENDER_STAGE_TIMES: events of the last such frame
+    bool stage_events_valid = false;
     ~rtb_scene() {
         cudaSetDevice(device);
         for (void *p : allocs) cudaFree(p);
         if (stage) cudaFree(stage);
+        if (wf_state) cudaFree(wf_state);
+        for (auto &e : stage_events) cudaEventDestroy(e);
         if (queue_heads) cudaFree(queue_heads);
         for (auto &s : streams) if (s) cudaStreamDestroy(s);
         for (auto &e : ev) if (e) cudaEventDestroy(e);
@@ -287,7 +295,27 @@ int rtb_render_device(rtb_scene *scene, const rtb_render_params *p, float *d_acc
     L.d_accum = d_accum; L.d_rgb8 = d_rgb8; L.d_counters = d_counters;
     L.count_tests = (p->flags & RTB_RENDER_COUNTERS) != 0 && d_counters != nullptr;
     L.cull_mode = (p->flags & RTB_RENDER_REFERENCE_CULL) ? RTB_CULL_REFERENCE : RTB_CULL_GLOBAL;
-    rtb::launch_render(scene->d, L, (cudaStream_t) stream);
+    // Integrator: the wavefront (ray-queue) form unless the caller asks for the megakernel; RTB_CULL_REFERENCE only
+    // exists as a megakernel (the queue traverses with global-best culling).
+    const bool mega = (p->flags & (RTB_RENDER_REFERENCE_CULL | RTB_RENDER_MEGAKERNEL)) != 0 || scene->d.ray_depth < 1 || scene->d.ray_depth > 15;
+    if (mega || local_rows == 0) {
+        rtb::launch_render(scene->d, L, (cudaStream_t) stream);
+        scene->launches += local_rows ? 1 : 0;
+    } else {
+        const size_t need = rtb::wf_alloc_bytes(rtb::wf_slots(L), std::max(1, scene->d.ray_depth - 1));
+        if (scene->wf_bytes < need) {
+            // the previous state may still be in use by work queued on a caller's stream
+            if (scene->wf_state) { RTB_CUDA(cudaDeviceSynchronize()); cudaFree(scene->wf_state); }
+            scene->wf_state = nullptr;
+            scene->wf_bytes = 0;
+            RTB_CUDA(cudaMalloc(&scene->wf_state, need));
+            scene->wf_bytes = need;
+        }
+        const bool timed = (p->flags & RTB_RENDER_STAGE_TIMES) != 0;
+        rtb::launch_render_wavefront(scene->d, L, scene->wf_state, (cudaStream_t) stream, &scene->launches,
+                                     timed ? &scene->stage_events : nullptr);
+        scene->stage_events_valid = timed;
+    }
     RTB_CUDA(cudaGetLastError());
     return RTB_OK;
 }
@@ -308,15 +336,16 @@ int rtb_render(rtb_scene *scene, const rtb_render_params *p, float *accum, uint8
     uint8_t *d_rgb = (uint8_t *) (base + rgb_off);
     unsigned long long *d_cnt = (unsigned long long *) (base + cnt_off);
     cudaStream_t st = scene->streams[0];
-    RTB_CUDA(cudaMemsetAsync(d_cnt, 0, 32, st));
+    RTB_CUDA(cudaMemsetAsync(d_cnt, 0, 48, st));
     RTB_CUDA(cudaEventRecord(scene->ev[0], st));
+    const unsigned long long launches_before = scene->launches;
     rc = rtb_render_device(scene, p, d_accum, rgb8 ? d_rgb : nullptr, d_cnt, st);
     if (rc != RTB_OK) return rc;
     RTB_CUDA(cudaEventRecord(scene->ev[1], st));
     if (accum && accum_bytes) RTB_CUDA(cudaMemcpyAsync(accum, d_accum, accum_bytes, cudaMemcpyDeviceToHost, st));
     if (rgb8 && rgb_bytes) RTB_CUDA(cudaMemcpyAsync(rgb8, d_rgb, rgb_bytes, cudaMemcpyDeviceToHost, st));
-    unsigned long long c[4] = {0, 0, 0, 0};
-    RTB_CUDA(cudaMemcpyAsync(c, d_cnt, 32, cudaMemcpyDeviceToHost, st));
+    unsigned long long c[6] = {0, 0, 0, 0, 0, 0};
+    RTB_CUDA(cudaMemcpyAsync(c, d_cnt, 48, cudaMemcpyDeviceToHost, st));
     RTB_CUDA(cudaStreamSynchronize(st));
     RTB_CUDA(cudaGetLastError());
     if (stats) {
@@ -327,8 +356,35 @@ int rtb_render(rtb_scene *scene, const rtb_render_params *p, float *accum, uint8
         stats->light_pdf_queries = c[1];
         stats->box_tests = c[2];
         stats->tri_tests = c[3];
-        stats->launches = npix ? 1 : 0;
+        stats->light_box_tests = c[4];
+        stats->light_tri_tests = c[5];
+        stats->launches = scene->launches - launches_before;
     }
+    return RTB_OK;
+}
+
+unsigned long long rtb_scene_launches(const rtb_scene *scene) { return scene ? scene->launches : 0ull; }
+
+int rtb_scene_stage_ms(rtb_scene *scene, double *trace_ms, double *other_ms, unsigned long long *trace_launches) {
+    if (!scene || !scene->stage_events_valid || scene->stage_events.size() < 3) {
+        rtb::set_error("rtb_scene_stage_ms: the last render on this scene did not ask for RTB_RENDER_STAGE_TIMES");
+        return RTB_ERR_INVALID;
+    }
+    RTB_CUDA(cudaSetDevice(scene->device));
+    const auto &ev = scene->stage_events;
+    RTB_CUDA(cudaEventSynchronize(ev.back()));
+    double tr = 0.0, ot = 0.0;
+    const size_t iters = (ev.size() - 1) / 2;
+    for (size_t i = 0; i < iters; ++i) {
+        float a = 0.f, b = 0.f;
+        RTB_CUDA(cudaEventElapsedTime(&a, ev[2 * i], ev[2 * i + 1]));
+        RTB_CUDA(cudaEventElapsedTime(&b, ev[2 * i + 1], ev[2 * i + 2]));
+        tr += a;
+        ot += b;
+    }
+    if (trace_ms) *trace_ms = tr;
+    if (other_ms) *other_ms = ot;
+    if (trace_launches) *trace_launches = iters;
     return RTB_OK;
 }
 

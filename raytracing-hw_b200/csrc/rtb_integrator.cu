@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_render(const __grid_con
     const int lr = ty * kTileH + (lane >> 3);   // local (output) row
     int py = p.row_begin + lr;
     if (p.il_count > 1) py = p.row_begin + ((lr / p.il_rows) * p.il_count + p.il_index) * p.il_rows + lr % p.il_rows;
-    PathCounters pc = {0ull, 0ull, {0ull, 0ull}};
+    PathCounters pc = {0ull, 0ull, {0ull, 0ull}, {0ull, 0ull}};
     if (px < p.width && lr < p.local_rows && py < p.row_end) {
         const V3 sum = render_pixel<CULL, COUNT>(sc, px, py, p.width, p.height, p.samples, p.pixel0_seed, &pc);
         const size_t o = ((size_t) lr * p.width + px) * 3;
@@ -40,9 +40,9 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock) k_render(const __grid_con
         }
     }
     if (p.d_counters) {
-        unsigned long long c[4] = {pc.rays, pc.light_queries, pc.tests.box, pc.tests.tri};
+        unsigned long long c[6] = {pc.rays, pc.light_queries, pc.tests.box + pc.light.box, pc.tests.tri + pc.light.tri, pc.light.box, pc.light.tri};
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < 6; ++k) {
             for (int o = 16; o > 0; o >>= 1) c[k] += __shfl_down_sync(0xffffffffu, c[k], o);
             if (lane == 0 && c[k]) atomicAdd(&p.d_counters[k], c[k]);
         }

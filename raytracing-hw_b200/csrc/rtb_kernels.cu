@@ -3,6 +3,8 @@
 // Compiled with --fmad=false (decision-exact float arithmetic, see rtb_device.cuh).
 #include "rtb_kernels.cuh"
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include "rtb_shade.cuh"
 #include "rtb_trace.cuh"
 
@@ -58,14 +60,17 @@ template <bool COUNT>
 __global__ void __launch_bounds__(128) k_closest_hit_queue(const __grid_constant__ DScene sc, const float *__restrict__ rays6, unsigned n,
                                                            unsigned *__restrict__ queue_head, int *__restrict__ id,
                                                            float *__restrict__ t, float *__restrict__ u, float *__restrict__ v,
-                                                           uint8_t *__restrict__ inside, unsigned long long *__restrict__ counters) {
-    Counters cnt = {0ull, 0ull};
+                                                           uint8_t *__restrict__ inside, unsigned long long *__restrict__ counters,
+                                                           const TracePolicy pol) {
+    QueueCounters cnt = {0ull, 0ull, 0ull};
     trace_persistent<COUNT>(
         sc.bvh, n, queue_head,
-        [&](unsigned i, Ray &r) {
+        [&](unsigned i, Ray &r, unsigned &tag) {
             const float2 *rp = reinterpret_cast<const float2 *>(rays6 + (size_t) i * 6);
             const float2 r0 = __ldg(rp), r1 = __ldg(rp + 1), r2 = __ldg(rp + 2);
             make_ray(r, r0.x, r0.y, r1.x, r1.y, r2.x, r2.y);
+            tag = i;
+            return true;
         },
         [&](unsigned i, const Ray &r, const Hit &h) {
             const bool ok = h.id >= 0;
@@ -85,7 +90,7 @@ __global__ void __launch_bounds__(128) k_closest_hit_queue(const __grid_constant
                 inside[i] = in;
             }
         },
-        &cnt);
+        &cnt, pol);
     if (COUNT) {
         for (int o = 16; o > 0; o >>= 1) {
             cnt.box += __shfl_down_sync(0xffffffffu, cnt.box, o);
@@ -96,6 +101,27 @@ __global__ void __launch_bounds__(128) k_closest_hit_queue(const __grid_constant
             atomicAdd(&counters[1], cnt.tri);
         }
     }
+}
+
+TracePolicy trace_policy() {
+    static TracePolicy pol = [] {
+        TracePolicy p = {8, 1, 1};
+        if (const char *e = std::getenv("RTB_TRACE_POLICY")) {
+            int a = 0, b = 0, c = 0;
+            if (std::sscanf(e, "%d,%d,%d", &a, &b, &c) == 3 && a >= 1 && a <= 32 && b >= 1 && c >= 1) p = {a, b, c};
+        }
+        return p;
+    }();
+    return pol;
+}
+
+int persistent_blocks_per_sm() {
+    static int v = [] {
+        int b = 8;
+        if (const char *e = std::getenv("RTB_TRACE_BLOCKS")) b = std::max(1, std::min(16, std::atoi(e)));
+        return b;
+    }();
+    return v;
 }
 
 int persistent_grid(int threads_per_block, int blocks_per_sm) {
@@ -116,9 +142,9 @@ void launch_closest_hit(const DScene &sc, const float *d_rays6, size_t n, int cu
     const unsigned block = 128;
     if (cull_mode == 1 && d_queue_head != nullptr && n < 0xFFFFFF00u) {
         cudaMemsetAsync(d_queue_head, 0, sizeof(unsigned), stream);
-        const unsigned pg = (unsigned) std::min<size_t>((n + block - 1) / block, (size_t) persistent_grid(block, 8));
-        if (d_counters) k_closest_hit_queue<true><<<pg, block, 0, stream>>>(sc, d_rays6, (unsigned) n, d_queue_head, d_id, d_t, d_u, d_v, d_inside, d_counters);
-        else k_closest_hit_queue<false><<<pg, block, 0, stream>>>(sc, d_rays6, (unsigned) n, d_queue_head, d_id, d_t, d_u, d_v, d_inside, d_counters);
+        const unsigned pg = (unsigned) std::min<size_t>((n + block - 1) / block, (size_t) persistent_grid(block, persistent_blocks_per_sm()));
+        if (d_counters) k_closest_hit_queue<true><<<pg, block, 0, stream>>>(sc, d_rays6, (unsigned) n, d_queue_head, d_id, d_t, d_u, d_v, d_inside, d_counters, trace_policy());
+        else k_closest_hit_queue<false><<<pg, block, 0, stream>>>(sc, d_rays6, (unsigned) n, d_queue_head, d_id, d_t, d_u, d_v, d_inside, d_counters, trace_policy());
         return;
     }
     const unsigned grid = (unsigned) ((n + block - 1) / block);

@@ -1,5 +1,6 @@
 // Kernel launchers (defined in rtb_kernels.cu / rtb_integrator.cu), called by the C ABI in rtb_api.cu.
 #pragma once
+#include <vector>
 #include "rtb_device.cuh"
 
 namespace rtb {
@@ -7,6 +8,7 @@ namespace rtb {
 void launch_closest_hit(const DScene &sc, const float *d_rays6, size_t n, int cull_mode, int *d_id, float *d_t, float *d_u,
                         float *d_v, uint8_t *d_inside, unsigned long long *d_counters, unsigned *d_queue_head, cudaStream_t stream);
 int persistent_grid(int threads_per_block, int blocks_per_sm);
+int persistent_blocks_per_sm();   // CTAs per SM of the persistent queue kernels (RTB_TRACE_BLOCKS overrides)
 
 void launch_light_pdf(const DScene &sc, const float *d_rays6, size_t n, float *d_pdf, cudaStream_t stream);
 
@@ -18,11 +20,17 @@ struct RenderLaunch {
     unsigned pixel0_seed;
     float *d_accum;                     // (row_end-row_begin) x width x 3, may be null
     uint8_t *d_rgb8;                    // same extent, may be null
-    unsigned long long *d_counters;     // 4 x u64 {rays, light queries, box, tri} or null
+    unsigned long long *d_counters;     // 6 x u64 {rays, light queries, box, tri, light box, light tri} or null
     bool count_tests;                   // also count box / triangle tests (slower instantiation)
     int cull_mode;                      // RTB_CULL_*
 };
 void launch_render(const DScene &sc, const RenderLaunch &p, cudaStream_t stream);
+// wavefront (ray-queue) integrator, rtb_wavefront.cu; `state` = wf_alloc_bytes() bytes of device memory
+unsigned wf_slots(const RenderLaunch &p);
+size_t wf_alloc_bytes(unsigned n_slots, int depth_cap);
+// stage_events (may be null): filled with events bracketing every k_wf_trace launch, see rtb_scene_stage_ms()
+void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *state, cudaStream_t stream, unsigned long long *launches,
+                             std::vector<cudaEvent_t> *stage_events);
 void launch_resolve(const float *d_accum, size_t n_pixels, int samples, uint8_t *d_rgb8, cudaStream_t stream);
 
 }  // namespace rtb

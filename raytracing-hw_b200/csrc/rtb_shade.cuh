@@ -406,7 +406,8 @@ struct Bounce {   // what Scene::intersect needs after its child returns (scene.
 
 struct PathCounters {
     unsigned long long rays, light_queries;
-    Counters tests;
+    Counters tests;   // closest-hit traversal (scene BVH)
+    Counters light;   // all-hits light queries (light BVH)
 };
 
 // Scene::intersect (scene.cpp:71-156) for one camera sample: returns intersection.color of the root call.
@@ -445,7 +446,7 @@ RTB_HD V3 trace_path(const DScene &sc, Ray r, Rng &g, PathCounters *pc) {
             if (dot(dir, Ng) <= 0.f) break;
             Ns = Ng;
         }
-        const float pdf = pdf_direction<COUNT>(sc, pos, Ns, eye, rough2, dir, COUNT ? &pc->tests : nullptr, &pc->light_queries);
+        const float pdf = pdf_direction<COUNT>(sc, pos, Ns, eye, rough2, dir, COUNT ? &pc->light : nullptr, &pc->light_queries);
         if (pdf <= 0.f || pdf != pdf) break;
         // the factors of scene.cpp:134-154, evaluated now (they only depend on this vertex)
         const V3 half = normal(dir - rd);
@@ -477,7 +478,8 @@ RTB_HD V3 trace_path(const DScene &sc, Ray r, Rng &g, PathCounters *pc) {
 }
 
 // Camera::cast_in_pixel (camera.cpp:49-62) + Ray::Ray
-RTB_HD void camera_ray(const DScene &sc, int px, int py, int width, int height, float ox, float oy, Ray &r) {
+// camera_dir: the un-normalised direction handed to Ray::Ray
+RTB_HD V3 camera_dir(const DScene &sc, int px, int py, int width, int height, float ox, float oy) {
     const float tx = (2.f * ((float) px + 0.5f + ox) / (float) width - 1.f) * sc.cam_tan_half_fov[0];
     const float ty = -(2.f * ((float) py + 0.5f + oy) / (float) height - 1.f) * sc.cam_tan_half_fov[1];
     const float tz = 1.f;
@@ -485,6 +487,10 @@ RTB_HD void camera_ray(const DScene &sc, int px, int py, int width, int height, 
     d = d + tx * V3{sc.cam_axes[0], sc.cam_axes[1], sc.cam_axes[2]};
     d = d + ty * V3{sc.cam_axes[3], sc.cam_axes[4], sc.cam_axes[5]};
     d = d + tz * V3{sc.cam_axes[6], sc.cam_axes[7], sc.cam_axes[8]};
+    return d;
+}
+RTB_HD void camera_ray(const DScene &sc, int px, int py, int width, int height, float ox, float oy, Ray &r) {
+    const V3 d = camera_dir(sc, px, py, width, height, ox, oy);
     make_ray(r, sc.cam_pos[0], sc.cam_pos[1], sc.cam_pos[2], d.x, d.y, d.z);
 }
 

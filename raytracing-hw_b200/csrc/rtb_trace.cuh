@@ -16,22 +16,37 @@
 
 namespace rtb {
 
-constexpr int kRefillMin = 8;   // refill as soon as this many lanes are idle (or nothing else is runnable)
+struct TracePolicy;
+TracePolicy trace_policy();   // rtb_kernels.cu
 
-// Fetch(idx, Ray&) loads ray `idx` (normalising as Ray::Ray does); Emit(idx, ray, hit) stores its result.
+struct QueueCounters {
+    unsigned long long box, tri, rays;
+};
+
+// Phase vote of a warp iteration: refill when at least `refill_min` lanes are idle (or nothing else is runnable);
+// otherwise the node phase when lanes_in_node_phase * w_node >= lanes_in_triangle_phase * w_leaf, else the triangle
+// phase.  A node step costs ~2.5x the instructions of a triangle step, so waiting triangle lanes are cheaper to serve
+// early: the default weights come from the sweep in profiles/ (RTB_TRACE_POLICY="refill,w_node,w_leaf" overrides).
+struct TracePolicy {
+    int refill_min, w_node, w_leaf;
+};
+
+// Fetch(idx, Ray&, tag&) loads queue entry `idx` (normalising as Ray::Ray does) and returns false when the entry holds
+// no ray (a finished slot of the wavefront integrator); Emit(tag, ray, hit) stores the result of the entry's ray.
 template <bool COUNT, class Fetch, class Emit>
-__device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsigned *queue_head, Fetch fetch, Emit emit, Counters *cnt) {
+__device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsigned *queue_head, Fetch fetch, Emit emit, QueueCounters *cnt, const TracePolicy pol) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     int s_link[kMaxStack + 1];
     float s_m[kMaxStack + 1];
     s_link[0] = kDoneLink;
-    s_m[0] = 0.f;
+    s_m[0] = -1.f;
     int sp = 1;
     int link = kDoneLink;          // >= 0 internal node pending; leaf link: triangles [tri_i, tri_end) pending; kDoneLink: no ray
     int tri_i = 0, tri_end = 0;
-    unsigned idx = 0;
+    unsigned tag = 0;
     bool have_ray = false, exhausted = false;
+    float omax = 0.f;
     Ray r;
     Hit best;
     float cull = 0.f;
@@ -54,7 +69,7 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
             --sp;
             l = s_link[sp];
             m = s_m[sp];
-        } while (m > cull);      // the sentinel carries m = 0
+        } while (m > cull);      // the sentinel carries m = -1
         if (l == kDoneLink) sp = 1;
         set_link(l);
     };
@@ -66,38 +81,41 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
         const unsigned mR = __ballot_sync(FULL, wantR), mN = __ballot_sync(FULL, wantN), mL = __ballot_sync(FULL, wantL);
         if ((mR | mN | mL) == 0u) break;
         const int cR = __popc(mR), cN = __popc(mN), cL = __popc(mL);
-        if (cR >= kRefillMin || (cN == 0 && cL == 0)) {
+        if (cR >= pol.refill_min || (cN == 0 && cL == 0)) {
             // ---- refill phase: store finished results, claim new rays
             const int leader = __ffs(mR) - 1;
             unsigned base = 0;
             if (lane == leader) base = atomicAdd(queue_head, (unsigned) cR);
             base = __shfl_sync(FULL, base, leader);
             if (wantR) {
-                if (have_ray) emit(idx, r, best);
-                idx = base + (unsigned) __popc(mR & ((1u << lane) - 1u));
+                if (have_ray) emit(tag, r, best);
+                const unsigned idx = base + (unsigned) __popc(mR & ((1u << lane) - 1u));
                 if (idx < n) {
-                    have_ray = true;
-                    fetch(idx, r);
-                    best.t = kFar; best.u = 0.f; best.v = 0.f; best.id = -1;
-                    cull = sq_threshold(kFar);
-                    float m0;
-                    if (COUNT) cnt->box += 1;
-                    if (box_test_sq(r, b.root_box[0], b.root_box[1], b.root_box[2], b.root_box[3], b.root_box[4], b.root_box[5], m0))
-                        set_link(b.root_link);
+                    have_ray = fetch(idx, r, tag);
+                    if (have_ray) {
+                        best.t = kFar; best.u = 0.f; best.v = 0.f; best.id = -1;
+                        omax = ray_omax(r);
+                        cull = cull_bound(kFar, omax);
+                        float m0;
+                        if (COUNT) cnt->box += 1;
+                        cnt->rays += 1;
+                        if (box_test_t(r, b.root_box[0], b.root_box[1], b.root_box[2], b.root_box[3], b.root_box[4], b.root_box[5], m0))
+                            set_link(b.root_link);
+                    }
                 } else {
                     have_ray = false;
                     exhausted = true;
                 }
             }
-        } else if (cN >= cL) {
+        } else if (cN * pol.w_node >= cL * pol.w_leaf) {
             // ---- node phase
             if (wantN) {
                 const DNode *np = b.nodes + link;
                 const float4 na = __ldg(&np->a), nb = __ldg(&np->b), nc = __ldg(&np->c);
                 const int4 nd = __ldg(&np->d);
                 float ml, mr;
-                const bool hl = box_test_sq(r, na.x, na.y, na.z, na.w, nb.x, nb.y, ml);
-                const bool hr = box_test_sq(r, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, mr);
+                const bool hl = box_test_t(r, na.x, na.y, na.z, na.w, nb.x, nb.y, ml);
+                const bool hr = box_test_t(r, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, mr);
                 if (COUNT) cnt->box += 2;
                 const float dax = nd.z == 0 ? r.d[0] : (nd.z == 1 ? r.d[1] : r.d[2]);
                 const bool left_first = dax > 0.f;   // bvh.cpp:183
@@ -128,7 +146,7 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
                     best.u = u;
                     best.v = v;
                     best.id = tri_i;
-                    cull = sq_threshold(t);
+                    cull = cull_bound(t, omax);
                 }
                 ++tri_i;
                 if (tri_i == tri_end) pop();

@@ -8,11 +8,18 @@
 //   leaf phase : every lane that holds a leaf tests one triangle per iteration (3 x LDG.128, straight-line
 //                Moller-Trumbore with a single IEEE division);
 //   pop        : next deferred sibling whose entry distance does not exceed the best hit.
-// Arithmetic contract unchanged (see rtb_device.cuh): the tests are restatements of AABB::intersect
+// Arithmetic contract unchanged (see rtb_device.cuh): the hit / miss decisions are restatements of AABB::intersect
 // (src/geometry/primitive.cpp:146-208) and Primitive::intersect (src/geometry/primitive.cpp:17-57) with identical
-// rounding; only control flow is predicated.  The sqrtf of the entry distance (primitive.cpp:207) is never taken:
-// `sqrtf(m) > best.t` is decided exactly as `m > sq_threshold(best.t)`, where sq_threshold(b) is the largest float
-// whose correctly rounded square root is <= b (recomputed only when the best hit changes).
+// rounding; only control flow is predicated.
+//
+// Culling (RTB_CULL_GLOBAL only).  The reference culls a box when its entry distance
+// length(hit point - origin) (primitive.cpp:207) exceeds the best hit.  Global-best culling may cull LESS than that
+// without changing the answer (the triangles tested stay a superset, in the same order), so the entry distance is
+// not evaluated at all: a box is culled when the ray parameter of its entry plane, tmax, exceeds
+//     cull_bound(best.t) = best.t * (1 + 1e-5) + 1e-6 * max|origin_i|,
+// which implies the reference's own distance exceeds best.t: the reference's distance differs from tmax by the
+// rounding of |d| (~1e-7 relative) and by the cancellation in (o + tmax*d) - o (<= 2 ulp of max(|o_i|, |c_i|) per
+// axis).  box_test_sq / sq_threshold (the exact squared-distance form) remain for reference and tests.
 #pragma once
 #include "rtb_device.cuh"
 
@@ -65,6 +72,37 @@ RTB_HD bool box_test_sq(const Ray &r, float mnx, float mny, float mnz, float mxx
     return inside || !bad;
 }
 
+// AABB::intersect, predicated, without the entry distance.  hit <=> the reference returns a value; tmax = the ray
+// parameter of the candidate plane (primitive.cpp:176-190), -1 when the origin is inside the box.
+RTB_HD bool box_test_t(const Ray &r, float mnx, float mny, float mnz, float mxx, float mxy, float mxz, float &tmax) {
+    const bool lo0 = r.o[0] < mnx, hi0 = r.o[0] > mxx;
+    const bool lo1 = r.o[1] < mny, hi1 = r.o[1] > mxy;
+    const bool lo2 = r.o[2] < mnz, hi2 = r.o[2] > mxz;
+    const float pl0 = lo0 ? mnx : mxx, pl1 = lo1 ? mny : mxy, pl2 = lo2 ? mnz : mxz;
+    const bool out0 = lo0 || hi0, out1 = lo1 || hi1, out2 = lo2 || hi2;   // quadrant != Mid
+    const float t0 = (out0 && r.d[0] != 0.f) ? (pl0 - r.o[0]) * r.inv[0] : -1.f;
+    const float t1 = (out1 && r.d[1] != 0.f) ? (pl1 - r.o[1]) * r.inv[1] : -1.f;
+    const float t2 = (out2 && r.d[2] != 0.f) ? (pl2 - r.o[2]) * r.inv[2] : -1.f;
+    const bool w1 = t0 < t1;                 // whichPlane = 1 (unless 2 wins)
+    float tm = w1 ? t1 : t0;
+    const bool w2 = tm < t2;                 // whichPlane = 2
+    tm = w2 ? t2 : tm;
+    const float c0 = r.o[0] + tm * r.d[0];
+    const float c1 = r.o[1] + tm * r.d[1];
+    const float c2 = r.o[2] + tm * r.d[2];
+    const bool bad0 = (c0 < mnx) || (c0 > mxx);
+    const bool bad1 = (c1 < mny) || (c1 > mxy);
+    const bool bad2 = (c2 < mnz) || (c2 > mxz);
+    // the coordinate of whichPlane itself is not checked (primitive.cpp:195-203)
+    const bool bad = ((w1 || w2) && bad0) || ((!w1 || w2) && bad1) || (!w2 && bad2) || (tm < 0.f);
+    const bool inside = !(out0 || out1 || out2);
+    tmax = inside ? -1.f : tm;
+    return inside || !bad;
+}
+// see the header comment: tmax > cull_bound(best.t, omax) implies the reference's entry distance > best.t
+RTB_HD float ray_omax(const Ray &r) { return fmaxf(fmaxf(fabsf(r.o[0]), fabsf(r.o[1])), fabsf(r.o[2])); }
+RTB_HD float cull_bound(float best_t, float omax) { return best_t * 1.00001f + 1e-6f * omax; }
+
 // Primitive::intersect, straight-line: one division, rejections folded into a flag with the reference's NaN
 // behaviour (every rejection is a comparison that is false for NaN).
 RTB_HD bool tri_test_flat(const Ray &r, const float4 q0, const float4 q1, const float4 q2, float &t, float &u, float &v) {
@@ -108,14 +146,15 @@ RTB_HD bool closest_hit_global(const DBvh &b, const Ray &r, Hit &best, Counters 
     best.v = 0.f;
     float m0;
     if (COUNT) cnt->box += 1;
-    if (!box_test_sq(r, b.root_box[0], b.root_box[1], b.root_box[2], b.root_box[3], b.root_box[4], b.root_box[5], m0)) return false;
+    if (!box_test_t(r, b.root_box[0], b.root_box[1], b.root_box[2], b.root_box[3], b.root_box[4], b.root_box[5], m0)) return false;
 
     int s_link[kMaxStack + 1];
     float s_m[kMaxStack + 1];
     s_link[0] = kDoneLink;
-    s_m[0] = 0.f;
+    s_m[0] = -1.f;
     int sp = 1;
-    float cull = sq_threshold(kFar);   // squared-distance image of best.t
+    const float omax = ray_omax(r);
+    float cull = cull_bound(kFar, omax);   // image of best.t for the entry-plane parameter
     int link = b.root_link;
 
     while (link != kDoneLink) {
@@ -125,8 +164,8 @@ RTB_HD bool closest_hit_global(const DBvh &b, const Ray &r, Hit &best, Counters 
             const float4 na = ldg(&np->a), nb = ldg(&np->b), nc = ldg(&np->c);
             const int4 nd = ldg(&np->d);
             float ml, mr;
-            const bool hl = box_test_sq(r, na.x, na.y, na.z, na.w, nb.x, nb.y, ml);
-            const bool hr = box_test_sq(r, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, mr);
+            const bool hl = box_test_t(r, na.x, na.y, na.z, na.w, nb.x, nb.y, ml);
+            const bool hr = box_test_t(r, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, mr);
             if (COUNT) cnt->box += 2;
             const float dax = nd.z == 0 ? r.d[0] : (nd.z == 1 ? r.d[1] : r.d[2]);
             const bool left_first = dax > 0.f;   // bvh.cpp:183
@@ -147,7 +186,7 @@ RTB_HD bool closest_hit_global(const DBvh &b, const Ray &r, Hit &best, Counters 
                     --sp;
                     link = s_link[sp];
                     m = s_m[sp];
-                } while (m > cull);   // the sentinel carries m = 0: never culled
+                } while (m > cull);   // the sentinel carries m = -1: never culled
             }
         }
         if (link == kDoneLink) break;
@@ -165,7 +204,7 @@ RTB_HD bool closest_hit_global(const DBvh &b, const Ray &r, Hit &best, Counters 
                     best.u = u;
                     best.v = v;
                     best.id = i;
-                    cull = sq_threshold(t);
+                    cull = cull_bound(t, omax);
                 }
             }
         }

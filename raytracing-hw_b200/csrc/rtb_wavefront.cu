@@ -1,0 +1,275 @@
+// Wavefront integrator (sm_100a): Scene::render (src/core/scene.cpp:17-65) as a ray queue.
+//
+//   k_wf_init    : one thread per slot (pixel): engine seed, first jitter, first primary ray     (scene.cpp:34-39)
+//   k_wf_trace   : persistent warps; lanes pull the active slots' rays from a queue and run the voted node /
+//                  triangle phases of rtb_trace.cuh (BVH::intersect, src/core/bvh.cpp:177-243)
+//   k_wf_shade   : one thread per active slot: Scene::intersect's vertex (scene.cpp:85-154) on the hit just found,
+//                  next direction from the slot's own sample stream, fold + accumulate + next sample at a path's end
+//   k_wf_count / k_wf_scan / k_wf_scatter : ORDER-PRESERVING compaction of the active list (finished pixels leave;
+//                  neighbouring pixels stay neighbours, so state loads stay coalesced)
+//
+// The host enqueues samples x ray_depth iterations (the most closest-hit rays any pixel can need) without ever
+// synchronising: every kernel reads the live count of its list from device memory, so iterations after the last
+// pixel finished cost an empty launch.  See rtb_wavefront.cuh for the state layout and the ncu evidence.
+#include "rtb_wavefront.cuh"
+
+#include <algorithm>
+#include <vector>
+#include "rtb_trace.cuh"
+
+namespace rtb {
+
+namespace {
+constexpr int kShadeBlock = 128;
+constexpr int kCompactBlock = 1024;
+
+__global__ void __launch_bounds__(256) k_wf_init(const __grid_constant__ DScene sc, const RenderLaunch p, const WfState w,
+                                                 unsigned *__restrict__ list, unsigned *__restrict__ n_list, unsigned *__restrict__ queue_head) {
+    const unsigned slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot == 0) {
+        *n_list = w.n_slots;
+        *queue_head = 0u;
+    }
+    if (slot < w.n_slots) list[slot] = wf_init_slot(sc, p, w, slot);
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_wf_trace(const __grid_constant__ DScene sc, const WfState w, const unsigned *__restrict__ list,
+                                                  const unsigned *__restrict__ n_list, unsigned *__restrict__ queue_head,
+                                                  unsigned long long *__restrict__ counters, const TracePolicy pol) {
+    const unsigned n = *n_list;
+    if (n == 0) return;
+    QueueCounters cnt = {0ull, 0ull, 0ull};
+    trace_persistent<COUNT>(
+        sc.bvh, n, queue_head,
+        [&](unsigned i, Ray &r, unsigned &tag) {
+            const unsigned e = list[i];
+            if (e & kSlotDone) return false;
+            tag = e;
+            wf_load_ray(w, e, r);
+            return true;
+        },
+        [&](unsigned slot, const Ray &, const Hit &h) { w.hit[slot] = make_float4(h.t, h.u, h.v, u2f((uint32_t) h.id)); },
+        &cnt, pol);
+    if (counters) {
+        for (int o = 16; o > 0; o >>= 1) {
+            cnt.rays += __shfl_down_sync(0xffffffffu, cnt.rays, o);
+            if (COUNT) {
+                cnt.box += __shfl_down_sync(0xffffffffu, cnt.box, o);
+                cnt.tri += __shfl_down_sync(0xffffffffu, cnt.tri, o);
+            }
+        }
+        if ((threadIdx.x & 31) == 0) {
+            if (cnt.rays) atomicAdd(&counters[0], cnt.rays);
+            if (COUNT) {
+                atomicAdd(&counters[2], cnt.box);
+                atomicAdd(&counters[3], cnt.tri);
+            }
+        }
+    }
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(kShadeBlock) k_wf_shade(const __grid_constant__ DScene sc, const RenderLaunch p, const WfState w,
+                                                          unsigned *__restrict__ list, const unsigned *__restrict__ n_list,
+                                                          unsigned *__restrict__ queue_head) {
+    const unsigned n = *n_list;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *queue_head = 0u;   // the next k_wf_trace starts at the head of the list
+    PathCounters pc = {0ull, 0ull, {0ull, 0ull}, {0ull, 0ull}};
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const unsigned e = list[i];
+        if (e & kSlotDone) continue;
+        const unsigned ne = wf_shade_slot<COUNT>(sc, p, w, e, &pc);
+        if (ne != e) list[i] = ne;
+    }
+    if (p.d_counters) {
+        // d_counters: {rays, light queries, box, tri, light box, light tri}; box / tri are totals over both BVHs
+        unsigned long long c[3] = {pc.light_queries, pc.light.box, pc.light.tri};
+#pragma unroll
+        for (int k = 0; k < (COUNT ? 3 : 1); ++k) {
+            for (int o = 16; o > 0; o >>= 1) c[k] += __shfl_down_sync(0xffffffffu, c[k], o);
+            if ((threadIdx.x & 31) == 0 && c[k]) {
+                atomicAdd(&p.d_counters[k + 1], c[k]);
+                if (k > 0) atomicAdd(&p.d_counters[k + 3], c[k]);
+            }
+        }
+    }
+}
+
+// ---- order-preserving compaction: count per block, scan the block counts, scatter
+__global__ void __launch_bounds__(kCompactBlock) k_wf_count(const unsigned *__restrict__ list, const unsigned *__restrict__ n_list,
+                                                            unsigned *__restrict__ block_counts) {
+    __shared__ unsigned warp_sums[kCompactBlock / 32];
+    const unsigned n = *n_list;
+    const unsigned i = blockIdx.x * kCompactBlock + threadIdx.x;
+    const bool alive = i < n && !(list[i] & kSlotDone);
+    const unsigned m = __ballot_sync(0xffffffffu, alive);
+    if ((threadIdx.x & 31) == 0) warp_sums[threadIdx.x >> 5] = __popc(m);
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        unsigned v = warp_sums[threadIdx.x];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+        if (threadIdx.x == 0) block_counts[blockIdx.x] = v;
+    }
+}
+
+// one block: exclusive scan of the block counts in place; the total becomes the length of the output list
+__global__ void __launch_bounds__(1024) k_wf_scan(unsigned *__restrict__ block_counts, unsigned n_blocks, unsigned *__restrict__ n_out) {
+    __shared__ unsigned warp_sums[32];
+    __shared__ unsigned carry;
+    if (threadIdx.x == 0) carry = 0u;
+    __syncthreads();
+    for (unsigned base = 0; base < n_blocks; base += 1024) {
+        const unsigned i = base + threadIdx.x;
+        const unsigned v = i < n_blocks ? block_counts[i] : 0u;
+        unsigned inc = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+            if ((threadIdx.x & 31) >= (unsigned) o) inc += t;
+        }
+        if ((threadIdx.x & 31) == 31) warp_sums[threadIdx.x >> 5] = inc;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            unsigned s = warp_sums[threadIdx.x];
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned t = __shfl_up_sync(0xffffffffu, s, o);
+                if (threadIdx.x >= (unsigned) o) s += t;
+            }
+            warp_sums[threadIdx.x] = s;   // inclusive over warps
+        }
+        __syncthreads();
+        const unsigned warp_off = (threadIdx.x >> 5) ? warp_sums[(threadIdx.x >> 5) - 1] : 0u;
+        const unsigned c = carry;
+        if (i < n_blocks) block_counts[i] = c + warp_off + inc - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = c + warp_off + inc;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *n_out = carry;
+}
+
+__global__ void __launch_bounds__(kCompactBlock) k_wf_scatter(const unsigned *__restrict__ list, const unsigned *__restrict__ n_list,
+                                                              const unsigned *__restrict__ block_offsets, unsigned *__restrict__ out) {
+    __shared__ unsigned warp_sums[kCompactBlock / 32];
+    const unsigned n = *n_list;
+    const unsigned i = blockIdx.x * kCompactBlock + threadIdx.x;
+    const unsigned e = i < n ? list[i] : kSlotDone;
+    const bool alive = !(e & kSlotDone);
+    const unsigned m = __ballot_sync(0xffffffffu, alive);
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) warp_sums[warp] = __popc(m);
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        unsigned s = warp_sums[threadIdx.x];
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned t = __shfl_up_sync(0xffffffffu, s, o);
+            if (threadIdx.x >= (unsigned) o) s += t;
+        }
+        warp_sums[threadIdx.x] = s;
+    }
+    __syncthreads();
+    if (alive) {
+        const unsigned off = block_offsets[blockIdx.x] + (warp ? warp_sums[warp - 1] : 0u) + __popc(m & ((1u << lane) - 1u));
+        out[off] = e;
+    }
+}
+}  // namespace
+
+size_t wf_state_bytes(unsigned n_slots, int depth_cap) {
+    const size_t per_slot = 16 + 8 + 16 + 16 + 16 + (size_t) depth_cap * (16 + 16 + 4) + 2 * 4;
+    const size_t blocks = ((size_t) n_slots + kCompactBlock - 1) / kCompactBlock;
+    return per_slot * n_slots + blocks * 4 + 4096;
+}
+
+// Carves the state arrays out of one allocation (`base`, wf_state_bytes() bytes, 256-byte aligned).
+static void wf_carve(char *base, unsigned n_slots, int depth_cap, WfState &w, unsigned *lists[2], unsigned **block_counts, unsigned **scalars) {
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+        char *p = base + off;
+        off += (bytes + 255) / 256 * 256;
+        return p;
+    };
+    w.n_slots = n_slots;
+    w.depth_cap = depth_cap;
+    w.ray_a = (float4 *) take((size_t) n_slots * 16);
+    w.hit = (float4 *) take((size_t) n_slots * 16);
+    w.ctl = (uint4 *) take((size_t) n_slots * 16);
+    w.sum = (float4 *) take((size_t) n_slots * 16);
+    w.stk_e = (float4 *) take((size_t) n_slots * 16 * depth_cap);
+    w.stk_m = (float4 *) take((size_t) n_slots * 16 * depth_cap);
+    w.ray_b = (float2 *) take((size_t) n_slots * 8);
+    w.stk_a = (float *) take((size_t) n_slots * 4 * depth_cap);
+    lists[0] = (unsigned *) take((size_t) n_slots * 4);
+    lists[1] = (unsigned *) take((size_t) n_slots * 4);
+    *block_counts = (unsigned *) take((((size_t) n_slots + kCompactBlock - 1) / kCompactBlock) * 4);
+    *scalars = (unsigned *) take(64);
+}
+
+size_t wf_alloc_bytes(unsigned n_slots, int depth_cap) {
+    // every array is rounded up to 256 bytes by wf_carve: 12 arrays
+    return wf_state_bytes(n_slots, depth_cap) + 12 * 256;
+}
+
+unsigned wf_slots(const RenderLaunch &p) {
+    const long long tiles = (long long) ((p.width + kWfTileW - 1) / kWfTileW) * ((p.local_rows + kWfTileH - 1) / kWfTileH);
+    return (unsigned) (tiles * 32);
+}
+
+void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *state, cudaStream_t stream, unsigned long long *launches,
+                             std::vector<cudaEvent_t> *stage_events) {
+    if (p.local_rows <= 0 || p.width <= 0 || p.samples <= 0) return;
+    const unsigned n_slots = wf_slots(p);
+    const int depth_cap = std::max(1, sc.ray_depth - 1);
+    WfState w;
+    unsigned *lists[2], *block_counts, *scalars;
+    wf_carve((char *) state, n_slots, depth_cap, w, lists, &block_counts, &scalars);
+    unsigned *n_list[2] = {scalars, scalars + 1};
+    unsigned *queue_head = scalars + 2;
+    const unsigned n_blocks = (n_slots + kCompactBlock - 1) / kCompactBlock;
+    unsigned long long nl = 0;
+
+    int cur = 0;
+    auto compact = [&]() {
+        k_wf_count<<<n_blocks, kCompactBlock, 0, stream>>>(lists[cur], n_list[cur], block_counts);
+        k_wf_scan<<<1, 1024, 0, stream>>>(block_counts, n_blocks, n_list[cur ^ 1]);
+        k_wf_scatter<<<n_blocks, kCompactBlock, 0, stream>>>(lists[cur], n_list[cur], block_counts, lists[cur ^ 1]);
+        cur ^= 1;
+        nl += 3;
+    };
+
+    k_wf_init<<<(n_slots + 255) / 256, 256, 0, stream>>>(sc, p, w, lists[0], n_list[0], queue_head);
+    ++nl;
+    compact();   // drops the slots outside the canvas
+    const unsigned trace_grid = (unsigned) std::min<size_t>(((size_t) n_slots + 127) / 128, (size_t) persistent_grid(128, persistent_blocks_per_sm()));
+    const TracePolicy pol = trace_policy();
+    const unsigned shade_grid = (unsigned) std::min<size_t>(((size_t) n_slots + kShadeBlock - 1) / kShadeBlock, (size_t) persistent_grid(kShadeBlock, 16));
+    const long long iterations = (long long) p.samples * sc.ray_depth;
+    const int period = 16;   // iterations between compactions
+    // optional stage timing: events[2*it], events[2*it+1] bracket iteration it's k_wf_trace; events[2*iterations] ends the frame
+    size_t ev_i = 0;
+    auto mark = [&]() {
+        if (!stage_events) return;
+        if (ev_i == stage_events->size()) {
+            cudaEvent_t e;
+            cudaEventCreate(&e);
+            stage_events->push_back(e);
+        }
+        cudaEventRecord((*stage_events)[ev_i++], stream);
+    };
+    for (long long it = 0; it < iterations; ++it) {
+        mark();
+        if (p.count_tests) k_wf_trace<true><<<trace_grid, 128, 0, stream>>>(sc, w, lists[cur], n_list[cur], queue_head, p.d_counters, pol);
+        else k_wf_trace<false><<<trace_grid, 128, 0, stream>>>(sc, w, lists[cur], n_list[cur], queue_head, p.d_counters, pol);
+        mark();
+        if (p.count_tests) k_wf_shade<true><<<shade_grid, kShadeBlock, 0, stream>>>(sc, p, w, lists[cur], n_list[cur], queue_head);
+        else k_wf_shade<false><<<shade_grid, kShadeBlock, 0, stream>>>(sc, p, w, lists[cur], n_list[cur], queue_head);
+        nl += 2;
+        if ((it + 1) % period == 0 && it + 1 < iterations) compact();
+    }
+    mark();
+    if (stage_events) stage_events->resize(ev_i);   // (events beyond ev_i were created by an earlier, longer frame)
+    if (launches) *launches += nl;
+}
+
+
+}  // namespace rtb

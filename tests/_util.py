@@ -79,6 +79,7 @@ def devsim():
         L.devsim_closest_hit.argtypes = [C.POINTER(rtb.SceneDesc), vp, C.c_size_t, C.c_int, vp, vp, vp, vp, vp, vp]
         L.devsim_light_pdf.argtypes = [C.POINTER(rtb.SceneDesc), vp, C.c_size_t, vp]
         L.devsim_render.argtypes = [C.POINTER(rtb.SceneDesc), C.POINTER(rtb.RenderParams), vp, vp, vp]
+        L.devsim_render_wavefront.argtypes = [C.POINTER(rtb.SceneDesc), C.POINTER(rtb.RenderParams), vp, vp, vp]
         L.devsim_trace_path.argtypes = [C.POINTER(rtb.SceneDesc), vp, vp, C.c_uint, vp, C.POINTER(C.c_uint)]
         _devsim = L
     return _devsim
@@ -108,13 +109,18 @@ def devsim_light_pdf(hs, rays):
     return out
 
 
-def devsim_render(hs, width, height, samples, rows=None, pixel0_seed=1, reference_cull=False):
+def devsim_render(hs, width, height, samples, rows=None, pixel0_seed=1, reference_cull=False, wavefront=False, interleave=None):
     r0, r1 = rows if rows is not None else (0, height)
     p = rtb.RenderParams(width, height, samples, r0, r1, pixel0_seed, 0, 2 if reference_cull else 0)
-    accum = np.empty((r1 - r0, width, 3), np.float32)
-    rgb = np.empty((r1 - r0, width, 3), np.uint8)
+    n_rows = r1 - r0
+    if interleave is not None:
+        p.interleave_count, p.interleave_index, p.interleave_rows = interleave
+        n_rows = rtb.lib().rtb_render_local_rows(C.byref(p))
+    accum = np.empty((n_rows, width, 3), np.float32)
+    rgb = np.empty((n_rows, width, 3), np.uint8)
     cnt = np.zeros(4, np.uint64)
-    assert devsim().devsim_render(C.byref(hs.desc), C.byref(p), _p(accum), _p(rgb), _p(cnt)) == 0
+    fn = devsim().devsim_render_wavefront if wavefront else devsim().devsim_render
+    assert fn(C.byref(hs.desc), C.byref(p), _p(accum), _p(rgb), _p(cnt)) == 0, devsim().devsim_last_error()
     return dict(accum=accum, rgb=rgb, rays=int(cnt[0]), light_queries=int(cnt[1]), box_tests=int(cnt[2]), tri_tests=int(cnt[3]))
 
 

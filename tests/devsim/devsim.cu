@@ -3,6 +3,7 @@
 // without a GPU (tests/test_devsim.py).  TEST TOOLING ONLY: librtb.so neither links nor calls this, and nothing
 // here is a fallback for the C ABI (which fails with RTB_ERR_NO_DEVICE when no GPU is usable).
 #include "../../raytracing-hw_b200/csrc/rtb_layout.hpp"
+#include "../../raytracing-hw_b200/csrc/rtb_wavefront.cuh"
 
 #include <omp.h>
 
@@ -99,10 +100,10 @@ int devsim_render(const rtb_scene_desc *desc, const rtb_render_params *p, float 
     for (int lr = 0; lr < rows; ++lr) {
         const int py = p->row_begin + lr;
         for (int px = 0; px < p->width; ++px) {
-            PathCounters pc = {0, 0, {0, 0}};
+            PathCounters pc = {0, 0, {0, 0}, {0, 0}};
             const V3 sum = cull == 0 ? render_pixel<0, true>(s.d, px, py, p->width, p->height, p->samples, p->pixel0_seed, &pc)
                                      : render_pixel<1, true>(s.d, px, py, p->width, p->height, p->samples, p->pixel0_seed, &pc);
-            c0 += pc.rays; c1 += pc.light_queries; c2 += pc.tests.box; c3 += pc.tests.tri;
+            c0 += pc.rays; c1 += pc.light_queries; c2 += pc.tests.box + pc.light.box; c3 += pc.tests.tri + pc.light.tri;
             const size_t o = ((size_t) lr * p->width + px) * 3;
             if (accum) { accum[o] = sum.x; accum[o + 1] = sum.y; accum[o + 2] = sum.z; }
             if (rgb8) {
@@ -117,6 +118,65 @@ int devsim_render(const rtb_scene_desc *desc, const rtb_render_params *p, float 
     return 0;
 }
 
+// The wavefront integrator's per-slot steps (rtb_wavefront.cuh: wf_init_slot / wf_shade_slot -- the same functions the
+// k_wf_* kernels call) driven on host arrays, with the queue replaced by closest_hit_global per active slot.
+int devsim_render_wavefront(const rtb_scene_desc *desc, const rtb_render_params *p, float *accum, uint8_t *rgb8, unsigned long long *counters4) {
+    SimScene s;
+    if (!make_scene(desc, s, g_err)) return 1;
+    RenderLaunch L;
+    std::memset(&L, 0, sizeof(L));
+    L.width = p->width; L.height = p->height; L.samples = p->samples;
+    L.row_begin = p->row_begin; L.row_end = p->row_end;
+    L.il_count = p->interleave_count; L.il_index = p->interleave_index; L.il_rows = p->interleave_rows > 0 ? p->interleave_rows : 4;
+    {   // rows this call renders (same rule as rtb_render_local_rows)
+        const int rows = p->row_end - p->row_begin;
+        L.local_rows = rows;
+        if (p->interleave_count > 1) {
+            const int R = L.il_rows, blocks = (rows + R - 1) / R;
+            L.local_rows = 0;
+            for (int b = p->interleave_index; b < blocks; b += p->interleave_count) L.local_rows += std::min(R, rows - b * R);
+        }
+    }
+    L.pixel0_seed = p->pixel0_seed;
+    L.d_accum = accum; L.d_rgb8 = rgb8;
+    const unsigned n_slots = (unsigned) (((L.width + kWfTileW - 1) / kWfTileW) * ((L.local_rows + kWfTileH - 1) / kWfTileH) * 32);
+    const int cap = std::max(1, s.d.ray_depth - 1);
+    std::vector<float4> ray_a(n_slots), hit(n_slots), sum(n_slots), stk_e((size_t) n_slots * cap), stk_m((size_t) n_slots * cap);
+    std::vector<float2> ray_b(n_slots);
+    std::vector<uint4> ctl(n_slots);
+    std::vector<float> stk_a((size_t) n_slots * cap);
+    WfState w;
+    w.n_slots = n_slots; w.depth_cap = cap;
+    w.ray_a = ray_a.data(); w.ray_b = ray_b.data(); w.hit = hit.data(); w.ctl = ctl.data(); w.sum = sum.data();
+    w.stk_e = stk_e.data(); w.stk_m = stk_m.data(); w.stk_a = stk_a.data();
+    std::vector<unsigned> list(n_slots);
+    for (unsigned i = 0; i < n_slots; ++i) list[i] = wf_init_slot(s.d, L, w, i);
+    unsigned long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+    const long long iterations = (long long) p->samples * s.d.ray_depth;
+    for (long long it = 0; it < iterations; ++it) {
+#pragma omp parallel for schedule(dynamic, 64) reduction(+ : c0, c1, c2, c3)
+        for (long long i = 0; i < (long long) n_slots; ++i) {
+            const unsigned e = list[(size_t) i];
+            if (e & kSlotDone) continue;
+            Ray r;
+            wf_load_ray(w, e, r);
+            Hit h;
+            Counters c = {0, 0};
+            closest_hit_global<true>(s.d.bvh, r, h, &c);
+            w.hit[e] = make_float4(h.t, h.u, h.v, u2f((uint32_t) h.id));
+            PathCounters pc = {0, 0, {0, 0}, {0, 0}};
+            list[(size_t) i] = wf_shade_slot<true>(s.d, L, w, e, &pc);
+            c0 += 1; c1 += pc.light_queries; c2 += c.box + pc.light.box; c3 += c.tri + pc.light.tri;
+        }
+    }
+    for (unsigned i = 0; i < n_slots; ++i) {
+        int px, lr, py;
+        if (wf_slot_pixel(L, i, px, lr, py) && !(list[i] & kSlotDone)) { g_err = "a slot did not finish"; return 2; }
+    }
+    if (counters4) { counters4[0] = c0; counters4[1] = c1; counters4[2] = c2; counters4[3] = c3; }
+    return 0;
+}
+
 // one path for an explicit ray and engine seed (mirror of oracle/ref_harness.cpp: ref_trace_path)
 int devsim_trace_path(const rtb_scene_desc *desc, const float *o3, const float *d3, unsigned engine_seed, float *rgb3, unsigned *engine_after) {
     SimScene s;
@@ -125,7 +185,7 @@ int devsim_trace_path(const rtb_scene_desc *desc, const float *o3, const float *
     rng_seed(g, engine_seed);
     Ray r;
     make_ray(r, o3[0], o3[1], o3[2], d3[0], d3[1], d3[2]);
-    PathCounters pc = {0, 0, {0, 0}};
+    PathCounters pc = {0, 0, {0, 0}, {0, 0}};
     const V3 c = trace_path<0, false>(s.d, r, g, &pc);
     rgb3[0] = c.x; rgb3[1] = c.y; rgb3[2] = c.z;
     *engine_after = g.x;

@@ -74,6 +74,35 @@ def test_render_bit_exact(name, reference_cull, host_scene):
     assert out["rays"] >= W * H * 4
 
 
+@pytest.mark.parametrize("name", SCENES)
+def test_wavefront_steps_bit_exact(name, host_scene):
+    """the wavefront integrator's per-slot steps (rtb_wavefront.cuh), driven on the host, give the sums and bytes of
+    the reference's deterministic render -- and the same ray / light-query / test counts as the megakernel form"""
+    g = _util.load_golden(name)
+    hs = host_scene(name)
+    H, W, _ = g["render_accum"].shape
+    out = _util.devsim_render(hs, W, H, 4, pixel0_seed=1, wavefront=True)
+    same = np.all(out["accum"] == g["render_accum"], axis=-1)
+    assert same.all(), "%d of %d pixels differ" % (np.count_nonzero(~same), same.size)
+    assert np.array_equal(out["rgb"], g["render_rgb"])
+    mega = _util.devsim_render(hs, W, H, 4, pixel0_seed=1)
+    for k in ("rays", "light_queries", "box_tests", "tri_tests"):
+        assert out[k] == mega[k], k
+
+
+def test_wavefront_row_ranges_and_interleave(host_scene):
+    """slots map to the same pixels (and seeds) under a row range and under the multi-GPU row-block interleave"""
+    hs = host_scene("s7_4")
+    W, H, S = 40, 36, 3
+    full = _util.devsim_render(hs, W, H, S, wavefront=True)["accum"]
+    part = _util.devsim_render(hs, W, H, S, rows=(8, 29), wavefront=True)["accum"]
+    assert np.array_equal(part, full[8:29])
+    for idx in range(3):
+        il = _util.devsim_render(hs, W, H, S, wavefront=True, interleave=(3, idx, 4))["accum"]
+        rows = [r for r in range(H) if (r // 4) % 3 == idx]
+        assert np.array_equal(il, full[rows])
+
+
 def test_libm_known_answers():
     """glibc logf / powf / pow(x,5) restatements (csrc/rtb_libm.cuh) against the reference host's libm"""
     import os
