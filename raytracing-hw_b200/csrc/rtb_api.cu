@@ -152,6 +152,8 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
         if ((rc = upload(sc, tex, &sc->d.textures)) != RTB_OK) return fail(rc);
     }
     fill_scalars(desc, sc->d);
+    fill_lut(L.lut);
+    if ((rc = upload(sc, L.lut, &sc->d.lut)) != RTB_OK) return fail(rc);
 
     RTB_CUDA(cudaMalloc((void **) &sc->queue_heads, kQueueHeads * sizeof(unsigned)));
     for (auto &s : sc->streams) RTB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));

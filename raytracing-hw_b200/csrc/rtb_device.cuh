@@ -98,7 +98,10 @@ struct DScene {
     int ray_depth;
     float max_distance;
     float bg_color[3];
-    float srgb_lut[256];      // powf(i/255.f, 2.2f) evaluated by the HOST libm (primitive.h:208)
+    const float *lut;         // 512 floats in global memory (L1-resident gathers; a table in the kernel parameters would
+                              // serialise divergent indices in the constant cache):
+                              //   [0,256)   powf(i/255.f, 2.2f) evaluated by the HOST libm (primitive.h:208)
+                              //   [256,512) (float) i / 255.f   (IEEE division, primitive.h:190-200)
 };
 
 struct Ray {

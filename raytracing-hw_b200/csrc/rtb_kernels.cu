@@ -56,14 +56,14 @@ __global__ void __launch_bounds__(128) k_closest_hit(const __grid_constant__ DSc
 }
 
 // Persistent ray-queue variant (RTB_CULL_GLOBAL): see rtb_trace.cuh.  grid = a few CTAs per SM; lanes pull rays.
-template <bool COUNT>
-__global__ void __launch_bounds__(128) k_closest_hit_queue(const __grid_constant__ DScene sc, const float *__restrict__ rays6, unsigned n,
+template <bool COUNT, int MINB, int MODE>
+__global__ void __launch_bounds__(128, MINB) k_closest_hit_queue(const __grid_constant__ DScene sc, const float *__restrict__ rays6, unsigned n,
                                                            unsigned *__restrict__ queue_head, int *__restrict__ id,
                                                            float *__restrict__ t, float *__restrict__ u, float *__restrict__ v,
                                                            uint8_t *__restrict__ inside, unsigned long long *__restrict__ counters,
                                                            const TracePolicy pol) {
     QueueCounters cnt = {0ull, 0ull, 0ull};
-    trace_persistent<COUNT>(
+    trace_persistent<COUNT, MODE>(
         sc.bvh, n, queue_head,
         [&](unsigned i, Ray &r, unsigned &tag) {
             const float2 *rp = reinterpret_cast<const float2 *>(rays6 + (size_t) i * 6);
@@ -115,9 +115,18 @@ TracePolicy trace_policy() {
     return pol;
 }
 
+int trace_mode() {
+    static int v = [] {
+        int m = kDefaultTraceMode;
+        if (const char *e = std::getenv("RTB_TRACE_MODE")) m = std::atoi(e) != 0 ? 1 : 0;
+        return m;
+    }();
+    return v;
+}
+
 int persistent_blocks_per_sm() {
     static int v = [] {
-        int b = 8;
+        int b = kDefaultTraceBlocks;
         if (const char *e = std::getenv("RTB_TRACE_BLOCKS")) b = std::max(1, std::min(16, std::atoi(e)));
         return b;
     }();
@@ -142,9 +151,18 @@ void launch_closest_hit(const DScene &sc, const float *d_rays6, size_t n, int cu
     const unsigned block = 128;
     if (cull_mode == 1 && d_queue_head != nullptr && n < 0xFFFFFF00u) {
         cudaMemsetAsync(d_queue_head, 0, sizeof(unsigned), stream);
-        const unsigned pg = (unsigned) std::min<size_t>((n + block - 1) / block, (size_t) persistent_grid(block, persistent_blocks_per_sm()));
-        if (d_counters) k_closest_hit_queue<true><<<pg, block, 0, stream>>>(sc, d_rays6, (unsigned) n, d_queue_head, d_id, d_t, d_u, d_v, d_inside, d_counters, trace_policy());
-        else k_closest_hit_queue<false><<<pg, block, 0, stream>>>(sc, d_rays6, (unsigned) n, d_queue_head, d_id, d_t, d_u, d_v, d_inside, d_counters, trace_policy());
+        const int bps = persistent_blocks_per_sm();
+        const unsigned pg = (unsigned) std::min<size_t>((n + block - 1) / block, (size_t) persistent_grid(block, bps));
+#define RTB_LAUNCH_Q(COUNT, MINB, MODE) k_closest_hit_queue<COUNT, MINB, MODE><<<pg, block, 0, stream>>>(sc, d_rays6, (unsigned) n, d_queue_head, d_id, d_t, d_u, d_v, d_inside, d_counters, trace_policy())
+#define RTB_LAUNCH_QM(MODE)                                  \
+        if (d_counters) RTB_LAUNCH_Q(true, 8, MODE);         \
+        else if (bps <= 8) RTB_LAUNCH_Q(false, 8, MODE);     \
+        else if (bps <= 10) RTB_LAUNCH_Q(false, 10, MODE);   \
+        else if (bps <= 12) RTB_LAUNCH_Q(false, 12, MODE);   \
+        else RTB_LAUNCH_Q(false, 16, MODE)
+        if (trace_mode() == 0) { RTB_LAUNCH_QM(0); } else { RTB_LAUNCH_QM(1); }
+#undef RTB_LAUNCH_QM
+#undef RTB_LAUNCH_Q
         return;
     }
     const unsigned grid = (unsigned) ((n + block - 1) / block);

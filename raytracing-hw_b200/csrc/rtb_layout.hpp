@@ -132,6 +132,7 @@ struct HostLayout {
     std::vector<float4> material;           // DScene::mesh_material
     std::vector<double> normal_transform;   // DScene::mesh_normal_transform
     int n_meshes = 0;
+    std::vector<float> lut;                 // DScene::lut
 };
 
 inline bool build_layout(const rtb_scene_desc *desc, HostLayout &L, std::string &err) {
@@ -205,7 +206,13 @@ inline void fill_scalars(const rtb_scene_desc *desc, DScene &d) {
     d.ray_depth = desc->ray_depth;
     d.max_distance = desc->max_distance;
     std::memcpy(d.bg_color, desc->bg_color, 12);
-    for (int i = 0; i < 256; ++i) d.srgb_lut[i] = std::pow((float) i / 255.f, 2.2f);
+}
+inline void fill_lut(std::vector<float> &lut) {
+    lut.resize(512);
+    for (int i = 0; i < 256; ++i) {
+        lut[(size_t) i] = std::pow((float) i / 255.f, 2.2f);
+        lut[(size_t) 256 + i] = (float) i / 255.f;
+    }
 }
 inline void fill_bvh_scalars(const HostBvhOut &h, DBvh &d, uint32_t n_tris) {
     std::memcpy(d.root_box, h.root_box, 24);

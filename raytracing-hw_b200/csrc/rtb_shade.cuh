@@ -250,6 +250,10 @@ RTB_HD float pdf_direction(const DScene &sc, V3 point, V3 n, V3 eye, float alpha
 // ------------------------------------------------------------------------------------------------ textures
 // Texture::interpolate_sample (primitive.h:182-215), channels = 4 (tinygltf always expands), repeat wrap.
 // SRGB: per-tap pow(v, 2.2f) through the host-computed 256-entry table (same glibc powf as the reference).
+RTB_HD int wrap_index(int i, int n) {   // i % n for 0 <= i <= n + 1
+    i = i >= n ? i - n : i;
+    return i >= n ? i - n : i;
+}
 template <bool SRGB>
 RTB_HD void texture_sample(const DScene &sc, int tex, float px, float py, float out[4]) {
     const DTexture t = sc.textures[tex];
@@ -259,8 +263,9 @@ RTB_HD void texture_sample(const DScene &sc, int tex, float px, float py, float 
     py = py * (float) t.height;
     const int ix = (int) floorf(px), iy = (int) floorf(py);
     const float dx = px - floorf(px), dy = py - floorf(py);
-    const int x0 = ix % t.width, x1 = (ix + 1) % t.width;
-    const int y0 = iy % t.height, y1 = (iy + 1) % t.height;
+    // 0 <= ix <= width (px lies in [0,1] after the wrap), so `% width` is at most two conditional subtractions
+    const int x0 = wrap_index(ix, t.width), x1 = wrap_index(ix + 1, t.width);
+    const int y0 = wrap_index(iy, t.height), y1 = wrap_index(iy + 1, t.height);
     const uchar4 c00 = ldg(&t.texels[(size_t) y0 * t.width + x0]);   // (dx=0, dy=0)
     const uchar4 c01 = ldg(&t.texels[(size_t) y1 * t.width + x0]);   // (dx=0, dy=1)
     const uchar4 c10 = ldg(&t.texels[(size_t) y0 * t.width + x1]);   // (dx=1, dy=0)
@@ -271,9 +276,9 @@ RTB_HD void texture_sample(const DScene &sc, int tex, float px, float py, float 
     for (int i = 0; i < 3; ++i) {   // the alpha channel is never read by the hot path (.reduce())
         float a00, a01, a10, a11;
         if (SRGB) {
-            a00 = sc.srgb_lut[b00[i]]; a01 = sc.srgb_lut[b01[i]]; a10 = sc.srgb_lut[b10[i]]; a11 = sc.srgb_lut[b11[i]];
-        } else {
-            a00 = (float) b00[i] / 255.f; a01 = (float) b01[i] / 255.f; a10 = (float) b10[i] / 255.f; a11 = (float) b11[i] / 255.f;
+            a00 = ldg(&sc.lut[b00[i]]); a01 = ldg(&sc.lut[b01[i]]); a10 = ldg(&sc.lut[b10[i]]); a11 = ldg(&sc.lut[b11[i]]);
+        } else {   // (float) byte / 255.f, tabulated
+            a00 = ldg(&sc.lut[256 + b00[i]]); a01 = ldg(&sc.lut[256 + b01[i]]); a10 = ldg(&sc.lut[256 + b10[i]]); a11 = ldg(&sc.lut[256 + b11[i]]);
         }
         // interpolate_bilinear (primitive.h:158-161)
         out[i] = a00 * (1.f - dx) * (1.f - dy) + a01 * (1.f - dx) * dy + a10 * dx * (1.f - dy) + a11 * dx * dy;

@@ -31,128 +31,208 @@ struct TracePolicy {
     int refill_min, w_node, w_leaf;
 };
 
-// Fetch(idx, Ray&, tag&) loads queue entry `idx` (normalising as Ray::Ray does) and returns false when the entry holds
-// no ray (a finished slot of the wavefront integrator); Emit(tag, ray, hit) stores the result of the entry's ray.
-template <bool COUNT, class Fetch, class Emit>
-__device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsigned *queue_head, Fetch fetch, Emit emit, QueueCounters *cnt, const TracePolicy pol) {
-    const unsigned FULL = 0xffffffffu;
-    const int lane = threadIdx.x & 31;
-    int s_link[kMaxStack + 1];
-    float s_m[kMaxStack + 1];
-    s_link[0] = kDoneLink;
-    s_m[0] = -1.f;
-    int sp = 1;
-    int link = kDoneLink;          // >= 0 internal node pending; leaf link: triangles [tri_i, tri_end) pending; kDoneLink: no ray
-    int tri_i = 0, tri_end = 0;
-    unsigned tag = 0;
-    bool have_ray = false, exhausted = false;
-    float omax = 0.f;
+constexpr int kPopLink = (int) 0x8FFFFFFEu;    // "a pop is pending": big-leaf index 2^28-2, never allocated
+
+// One lane's traversal state and its steps.  RTB_HD so that tests/devsim can run the same state machine on the host.
+// States (by `link`): >= 0 internal node to visit; a leaf link while its triangles [tri_i, tri_end) are being tested;
+// kPopLink: the entries looked at by the last pop were all culled, pop again; kDoneLink: finished / no ray.
+//
+// The pop is branch-free and bounded: it looks at the two topmost deferred siblings at once (two independent
+// local-memory loads) and, if both are culled, leaves the lane in the kPopLink state for the next iteration.  ncu showed
+// the `do {} while (m > cull)` form running at 2 active lanes with a quarter of all stall samples on its dependent
+// loads (profiles/r01e_k_wf_trace_lines.txt).
+template <bool COUNT>
+struct LaneTraversal {
+    // the deferred-sibling stack lives in the caller's frame (dynamically indexed => local memory); keeping the arrays
+    // out of this struct lets every other member be promoted to registers
+    int *s_link;
+    float *s_m;
+    int sp;
+    int link;
+    int tri_i, tri_end;
+    float omax, cull;
     Ray r;
     Hit best;
-    float cull = 0.f;
-    best.t = kFar; best.u = 0.f; best.v = 0.f; best.id = -1;
-    for (int k = 0; k < 3; ++k) { r.o[k] = 0.f; r.d[k] = 0.f; r.inv[k] = 0.f; }
 
-    auto set_link = [&](int l) {
+    RTB_HD void reset(int *stack_link, float *stack_m) {
+        s_link = stack_link;
+        s_m = stack_m;
+        s_link[0] = kDoneLink;
+        s_m[0] = -1.f;          // the sentinel is never culled
+        sp = 1;
+        link = kDoneLink;
+        tri_i = tri_end = 0;
+        omax = 0.f;
+        cull = 0.f;
+        best.t = kFar; best.u = 0.f; best.v = 0.f; best.id = -1;
+        for (int k = 0; k < 3; ++k) { r.o[k] = 0.f; r.d[k] = 0.f; r.inv[k] = 0.f; }
+    }
+    RTB_HD bool wants_node() const { return link >= 0; }
+    RTB_HD bool wants_tri() const { return tri_i < tri_end; }
+    RTB_HD bool wants_pop() const { return link == kPopLink; }
+    RTB_HD bool finished() const { return link == kDoneLink; }
+
+    RTB_HD void set_link(const DBvh &b, int l) {
         link = l;
-        if (l < 0 && l != kDoneLink) {
+        if (l < 0 && l != kDoneLink && l != kPopLink) {
             int first, count;
             decode_leaf(b, l, first, count);
             tri_i = first;
             tri_end = first + count;
         }
-    };
-    auto pop = [&]() {
-        float m;
-        int l;
-        do {
-            --sp;
-            l = s_link[sp];
-            m = s_m[sp];
-        } while (m > cull);      // the sentinel carries m = -1
+    }
+    RTB_HD void pop(const DBvh &b) {
+        const int i1 = sp - 1, i2 = sp >= 2 ? sp - 2 : 0;
+        const int l1 = s_link[i1], l2 = s_link[i2];
+        const float m1 = s_m[i1], m2 = s_m[i2];
+        const bool k1 = !(m1 > cull), k2 = !(m2 > cull);
+        int l = k1 ? l1 : (k2 ? l2 : kPopLink);
+        sp = k1 ? i1 : i2;
         if (l == kDoneLink) sp = 1;
-        set_link(l);
-    };
+        set_link(b, l);
+    }
+    // `r` has been set: root box test (bvh.cpp:240)
+    template <class C>
+    RTB_HD void begin(const DBvh &b, C *cnt) {
+        best.t = kFar; best.u = 0.f; best.v = 0.f; best.id = -1;
+        omax = ray_omax(r);
+        cull = cull_bound(kFar, omax);
+        float m0;
+        if (COUNT) cnt->box += 1;
+        if (box_test_t(r, b.root_box[0], b.root_box[1], b.root_box[2], b.root_box[3], b.root_box[4], b.root_box[5], m0)) set_link(b, b.root_link);
+    }
+    template <class C>
+    RTB_HD void node_compute(const DBvh &b, const float4 na, const float4 nb, const float4 nc, const int4 nd, C *cnt) {
+        float ml, mr;
+        const bool hl = box_test_t(r, na.x, na.y, na.z, na.w, nb.x, nb.y, ml);
+        const bool hr = box_test_t(r, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, mr);
+        if (COUNT) cnt->box += 2;
+        const float dax = nd.z == 0 ? r.d[0] : (nd.z == 1 ? r.d[1] : r.d[2]);
+        const bool left_first = dax > 0.f;   // bvh.cpp:183
+        const int lA = left_first ? nd.x : nd.y, lB = left_first ? nd.y : nd.x;
+        const float mA = left_first ? ml : mr, mB = left_first ? mr : ml;
+        const bool vA = (left_first ? hl : hr) && !(mA > cull);
+        const bool vB = (left_first ? hr : hl) && !(mB > cull);
+        if (vA && vB) {
+            s_link[sp] = lB;
+            s_m[sp] = mB;
+            ++sp;
+            set_link(b, lA);
+        } else if (vA || vB) {
+            set_link(b, vA ? lA : lB);
+        } else {
+            pop(b);
+        }
+    }
+    template <class C>
+    RTB_HD void tri_compute(const DBvh &b, const float4 q0, const float4 q1, const float4 q2, C *cnt) {
+        float t, u, v;
+        if (COUNT) cnt->tri += 1;
+        if (tri_test_flat(r, q0, q1, q2, t, u, v) && t < best.t) {
+            best.t = t;
+            best.u = u;
+            best.v = v;
+            best.id = tri_i;
+            cull = cull_bound(t, omax);
+        }
+        ++tri_i;
+        if (tri_i == tri_end) pop(b);
+    }
+    template <class C>
+    RTB_HD void node_step(const DBvh &b, C *cnt) {
+        const DNode *np = b.nodes + link;
+        const float4 na = ldg(&np->a), nb = ldg(&np->b), nc = ldg(&np->c);
+        const int4 nd = ldg(&np->d);
+        node_compute(b, na, nb, nc, nd, cnt);
+    }
+    template <class C>
+    RTB_HD void tri_step(const DBvh &b, C *cnt) {
+        const float4 *tp = b.tris + (size_t) tri_i * 3;
+        const float4 q0 = ldg(tp), q1 = ldg(tp + 1), q2 = ldg(tp + 2);
+        tri_compute(b, q0, q1, q2, cnt);
+    }
+    // whatever the lane's state asks for (host drivers; the device loops below schedule the steps per warp)
+    template <class C>
+    RTB_HD void step(const DBvh &b, C *cnt) {
+        if (wants_pop()) pop(b);
+        else if (wants_node()) node_step(b, cnt);
+        else if (wants_tri()) tri_step(b, cnt);
+    }
+};
+
+#ifdef __CUDACC__
+// Fetch(idx, Ray&, tag&) loads queue entry `idx` (normalising as Ray::Ray does) and returns false when the entry holds
+// no ray (a finished slot of the wavefront integrator); Emit(tag, ray, hit) stores the result of the entry's ray.
+//
+// MODE 0 (voted phases): each warp iteration runs ONE phase chosen by vote (refill / node / triangle).
+// MODE 1 (unified step): each warp iteration serves EVERY lane: one fetch stage in which a lane loads its node
+//   (4 x LDG.128) or its triangle (3 x LDG.128) through the same instructions, then the node code for the lanes
+//   holding a node and the triangle code for the lanes holding a triangle.  Half the iterations per ray of MODE 0
+//   (a lane never waits for its phase to win a vote), so half the exposed memory latencies; see DESIGN.md.
+template <bool COUNT, int MODE, class Fetch, class Emit>
+__device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsigned *queue_head, Fetch fetch, Emit emit, QueueCounters *cnt, const TracePolicy pol) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    int stack_link[kMaxStack + 1];
+    float stack_m[kMaxStack + 1];
+    LaneTraversal<COUNT> L;
+    L.reset(stack_link, stack_m);
+    unsigned tag = 0;
+    bool have_ray = false, exhausted = false;
 
     while (true) {
-        const bool wantR = (link == kDoneLink) && !exhausted;
-        const bool wantN = link >= 0;
-        const bool wantL = (link < 0) && (link != kDoneLink);
-        const unsigned mR = __ballot_sync(FULL, wantR), mN = __ballot_sync(FULL, wantN), mL = __ballot_sync(FULL, wantL);
-        if ((mR | mN | mL) == 0u) break;
-        const int cR = __popc(mR), cN = __popc(mN), cL = __popc(mL);
-        if (cR >= pol.refill_min || (cN == 0 && cL == 0)) {
-            // ---- refill phase: store finished results, claim new rays
+        const bool wantR = L.finished() && !exhausted;
+        const bool busy = !L.finished();
+        const unsigned mR = __ballot_sync(FULL, wantR), mB = __ballot_sync(FULL, busy);
+        if ((mR | mB) == 0u) break;
+        const int cR = __popc(mR);
+        if (cR >= pol.refill_min || mB == 0u) {
+            // ---- refill: store finished results, claim new rays (warp-aggregated atomic)
             const int leader = __ffs(mR) - 1;
             unsigned base = 0;
             if (lane == leader) base = atomicAdd(queue_head, (unsigned) cR);
             base = __shfl_sync(FULL, base, leader);
             if (wantR) {
-                if (have_ray) emit(tag, r, best);
+                if (have_ray) emit(tag, L.r, L.best);
                 const unsigned idx = base + (unsigned) __popc(mR & ((1u << lane) - 1u));
                 if (idx < n) {
-                    have_ray = fetch(idx, r, tag);
+                    have_ray = fetch(idx, L.r, tag);
                     if (have_ray) {
-                        best.t = kFar; best.u = 0.f; best.v = 0.f; best.id = -1;
-                        omax = ray_omax(r);
-                        cull = cull_bound(kFar, omax);
-                        float m0;
-                        if (COUNT) cnt->box += 1;
                         cnt->rays += 1;
-                        if (box_test_t(r, b.root_box[0], b.root_box[1], b.root_box[2], b.root_box[3], b.root_box[4], b.root_box[5], m0))
-                            set_link(b.root_link);
+                        L.begin(b, cnt);
                     }
                 } else {
                     have_ray = false;
                     exhausted = true;
                 }
             }
-        } else if (cN * pol.w_node >= cL * pol.w_leaf) {
-            // ---- node phase
-            if (wantN) {
-                const DNode *np = b.nodes + link;
-                const float4 na = __ldg(&np->a), nb = __ldg(&np->b), nc = __ldg(&np->c);
-                const int4 nd = __ldg(&np->d);
-                float ml, mr;
-                const bool hl = box_test_t(r, na.x, na.y, na.z, na.w, nb.x, nb.y, ml);
-                const bool hr = box_test_t(r, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, mr);
-                if (COUNT) cnt->box += 2;
-                const float dax = nd.z == 0 ? r.d[0] : (nd.z == 1 ? r.d[1] : r.d[2]);
-                const bool left_first = dax > 0.f;   // bvh.cpp:183
-                const int lA = left_first ? nd.x : nd.y, lB = left_first ? nd.y : nd.x;
-                const float mA = left_first ? ml : mr, mB = left_first ? mr : ml;
-                const bool vA = (left_first ? hl : hr) && !(mA > cull);
-                const bool vB = (left_first ? hr : hl) && !(mB > cull);
-                if (vA && vB) {
-                    s_link[sp] = lB;
-                    s_m[sp] = mB;
-                    ++sp;
-                    set_link(lA);
-                } else if (vA || vB) {
-                    set_link(vA ? lA : lB);
-                } else {
-                    pop();
-                }
+            continue;
+        }
+        if (L.wants_pop()) L.pop(b);
+        const bool doN = L.wants_node(), doL = L.wants_tri();
+        if (MODE == 0) {
+            const int cN = __popc(__ballot_sync(FULL, doN)), cL = __popc(__ballot_sync(FULL, doL));
+            if (cN * pol.w_node >= cL * pol.w_leaf) {
+                if (doN) L.node_step(b, cnt);
+            } else {
+                if (doL) L.tri_step(b, cnt);
             }
         } else {
-            // ---- triangle phase: one triangle per lane
-            if (wantL) {
-                const float4 *tp = b.tris + (size_t) tri_i * 3;
-                const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
-                float t, u, v;
-                if (COUNT) cnt->tri += 1;
-                if (tri_test_flat(r, q0, q1, q2, t, u, v) && t < best.t) {
-                    best.t = t;
-                    best.u = u;
-                    best.v = v;
-                    best.id = tri_i;
-                    cull = cull_bound(t, omax);
-                }
-                ++tri_i;
-                if (tri_i == tri_end) pop();
+            // one fetch stage for both kinds of record
+            const float4 *p = doN ? reinterpret_cast<const float4 *>(b.nodes + L.link) : (b.tris + (size_t) L.tri_i * 3);
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a, c = a;
+            int4 d = make_int4(0, 0, 0, 0);
+            if (doN || doL) {
+                a = __ldg(p);
+                bb = __ldg(p + 1);
+                c = __ldg(p + 2);
             }
+            if (doN) d = __ldg(reinterpret_cast<const int4 *>(p + 3));
+            if (doN) L.node_compute(b, a, bb, c, d, cnt);
+            if (doL) L.tri_compute(b, a, bb, c, cnt);
         }
     }
 }
+#endif
 
 }  // namespace rtb

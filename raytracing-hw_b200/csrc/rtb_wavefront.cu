@@ -33,14 +33,14 @@ __global__ void __launch_bounds__(256) k_wf_init(const __grid_constant__ DScene 
     if (slot < w.n_slots) list[slot] = wf_init_slot(sc, p, w, slot);
 }
 
-template <bool COUNT>
-__global__ void __launch_bounds__(128) k_wf_trace(const __grid_constant__ DScene sc, const WfState w, const unsigned *__restrict__ list,
+template <bool COUNT, int MINB, int MODE>
+__global__ void __launch_bounds__(128, MINB) k_wf_trace(const __grid_constant__ DScene sc, const WfState w, const unsigned *__restrict__ list,
                                                   const unsigned *__restrict__ n_list, unsigned *__restrict__ queue_head,
                                                   unsigned long long *__restrict__ counters, const TracePolicy pol) {
     const unsigned n = *n_list;
     if (n == 0) return;
     QueueCounters cnt = {0ull, 0ull, 0ull};
-    trace_persistent<COUNT>(
+    trace_persistent<COUNT, MODE>(
         sc.bvh, n, queue_head,
         [&](unsigned i, Ray &r, unsigned &tag) {
             const unsigned e = list[i];
@@ -240,8 +240,10 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
     k_wf_init<<<(n_slots + 255) / 256, 256, 0, stream>>>(sc, p, w, lists[0], n_list[0], queue_head);
     ++nl;
     compact();   // drops the slots outside the canvas
-    const unsigned trace_grid = (unsigned) std::min<size_t>(((size_t) n_slots + 127) / 128, (size_t) persistent_grid(128, persistent_blocks_per_sm()));
+    const int bps = persistent_blocks_per_sm();
+    const unsigned trace_grid = (unsigned) std::min<size_t>(((size_t) n_slots + 127) / 128, (size_t) persistent_grid(128, bps));
     const TracePolicy pol = trace_policy();
+    const int mode = trace_mode();
     const unsigned shade_grid = (unsigned) std::min<size_t>(((size_t) n_slots + kShadeBlock - 1) / kShadeBlock, (size_t) persistent_grid(kShadeBlock, 16));
     const long long iterations = (long long) p.samples * sc.ray_depth;
     const int period = 16;   // iterations between compactions
@@ -258,8 +260,16 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
     };
     for (long long it = 0; it < iterations; ++it) {
         mark();
-        if (p.count_tests) k_wf_trace<true><<<trace_grid, 128, 0, stream>>>(sc, w, lists[cur], n_list[cur], queue_head, p.d_counters, pol);
-        else k_wf_trace<false><<<trace_grid, 128, 0, stream>>>(sc, w, lists[cur], n_list[cur], queue_head, p.d_counters, pol);
+#define RTB_LAUNCH_T(COUNT, MINB, MODE) k_wf_trace<COUNT, MINB, MODE><<<trace_grid, 128, 0, stream>>>(sc, w, lists[cur], n_list[cur], queue_head, p.d_counters, pol)
+#define RTB_LAUNCH_TM(MODE)                                      \
+        if (p.count_tests) RTB_LAUNCH_T(true, 8, MODE);          \
+        else if (bps <= 8) RTB_LAUNCH_T(false, 8, MODE);         \
+        else if (bps <= 10) RTB_LAUNCH_T(false, 10, MODE);       \
+        else if (bps <= 12) RTB_LAUNCH_T(false, 12, MODE);       \
+        else RTB_LAUNCH_T(false, 16, MODE)
+        if (mode == 0) { RTB_LAUNCH_TM(0); } else { RTB_LAUNCH_TM(1); }
+#undef RTB_LAUNCH_TM
+#undef RTB_LAUNCH_T
         mark();
         if (p.count_tests) k_wf_shade<true><<<shade_grid, kShadeBlock, 0, stream>>>(sc, p, w, lists[cur], n_list[cur], queue_head);
         else k_wf_shade<false><<<shade_grid, kShadeBlock, 0, stream>>>(sc, p, w, lists[cur], n_list[cur], queue_head);

@@ -77,6 +77,7 @@ def devsim():
         vp = C.c_void_p
         L.devsim_last_error.restype = C.c_char_p
         L.devsim_closest_hit.argtypes = [C.POINTER(rtb.SceneDesc), vp, C.c_size_t, C.c_int, vp, vp, vp, vp, vp, vp]
+        L.devsim_closest_hit_lane.argtypes = [C.POINTER(rtb.SceneDesc), vp, C.c_size_t, C.c_uint, vp, vp, vp, vp, vp]
         L.devsim_light_pdf.argtypes = [C.POINTER(rtb.SceneDesc), vp, C.c_size_t, vp]
         L.devsim_render.argtypes = [C.POINTER(rtb.SceneDesc), C.POINTER(rtb.RenderParams), vp, vp, vp]
         L.devsim_render_wavefront.argtypes = [C.POINTER(rtb.SceneDesc), C.POINTER(rtb.RenderParams), vp, vp, vp]
@@ -97,6 +98,19 @@ def devsim_closest_hit(hs, rays, cull):
     cnt = np.zeros(2, np.uint64)
     rc = devsim().devsim_closest_hit(C.byref(hs.desc), _p(rays), n, cull, _p(out["id"]), _p(out["t"]), _p(out["u"]), _p(out["v"]),
                                      _p(out["inside"]), _p(cnt))
+    assert rc == 0, devsim().devsim_last_error()
+    out["box_tests"], out["tri_tests"] = int(cnt[0]), int(cnt[1])
+    return out
+
+
+def devsim_closest_hit_lane(hs, rays, schedule_seed):
+    """the queue kernels' per-lane state machine (deferred leaves) on the host, phases drawn from `schedule_seed`"""
+    rays = np.ascontiguousarray(rays, np.float32)
+    n = rays.shape[0]
+    out = dict(id=np.empty(n, np.int32), t=np.empty(n, np.float32), u=np.empty(n, np.float32), v=np.empty(n, np.float32))
+    cnt = np.zeros(2, np.uint64)
+    rc = devsim().devsim_closest_hit_lane(C.byref(hs.desc), _p(rays), n, schedule_seed, _p(out["id"]), _p(out["t"]), _p(out["u"]),
+                                          _p(out["v"]), _p(cnt))
     assert rc == 0, devsim().devsim_last_error()
     out["box_tests"], out["tri_tests"] = int(cnt[0]), int(cnt[1])
     return out

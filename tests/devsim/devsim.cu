@@ -4,6 +4,7 @@
 // here is a fallback for the C ABI (which fails with RTB_ERR_NO_DEVICE when no GPU is usable).
 #include "../../raytracing-hw_b200/csrc/rtb_layout.hpp"
 #include "../../raytracing-hw_b200/csrc/rtb_wavefront.cuh"
+#include "../../raytracing-hw_b200/csrc/rtb_trace.cuh"
 
 #include <omp.h>
 
@@ -40,6 +41,8 @@ bool make_scene(const rtb_scene_desc *desc, SimScene &s, std::string &err) {
         s.tex[i] = {(const uchar4 *) desc->textures[i].rgba, desc->textures[i].width, desc->textures[i].height};
     s.d.textures = s.tex.data();
     fill_scalars(desc, s.d);
+    fill_lut(s.L.lut);
+    s.d.lut = s.L.lut.data();
     return true;
 }
 std::string g_err;
@@ -75,6 +78,35 @@ int devsim_closest_hit(const rtb_scene_desc *desc, const float *rays6, size_t n,
             }
             inside[i] = in;
         }
+    }
+    if (counters2) { counters2[0] = box; counters2[1] = tri; }
+    return 0;
+}
+
+// The queue kernels' per-lane state machine (rtb_trace.cuh: LaneTraversal, bounded branch-free pops) on the host.
+int devsim_closest_hit_lane(const rtb_scene_desc *desc, const float *rays6, size_t n, unsigned schedule_seed, int32_t *id, float *t,
+                            float *u, float *v, unsigned long long *counters2) {
+    SimScene s;
+    if (!make_scene(desc, s, g_err)) return 1;
+    unsigned long long box = 0, tri = 0;
+#pragma omp parallel for schedule(dynamic, 1024) reduction(+ : box, tri)
+    for (size_t i = 0; i < n; ++i) {
+        int stack_link[kMaxStack + 1];
+        float stack_m[kMaxStack + 1];
+        LaneTraversal<true> L;
+        L.reset(stack_link, stack_m);
+        make_ray(L.r, rays6[i * 6], rays6[i * 6 + 1], rays6[i * 6 + 2], rays6[i * 6 + 3], rays6[i * 6 + 4], rays6[i * 6 + 5]);
+        Counters c = {0, 0};
+        L.begin(s.d.bvh, &c);
+        (void) schedule_seed;
+        while (!L.finished()) L.step(s.d.bvh, &c);
+        box += c.box;
+        tri += c.tri;
+        const bool ok = L.best.id >= 0;
+        id[i] = ok ? L.best.id : -1;
+        if (t) t[i] = ok ? L.best.t : 0.f;
+        if (u) u[i] = ok ? L.best.u : 0.f;
+        if (v) v[i] = ok ? L.best.v : 0.f;
     }
     if (counters2) { counters2[0] = box; counters2[1] = tri; }
     return 0;

@@ -24,6 +24,23 @@ def test_closest_hit_bit_exact(name, cull, host_scene):
     assert np.array_equal(h["id"], g["cam_hit_id"]) and np.array_equal(h["t"], g["cam_hit_t"])
 
 
+@pytest.mark.parametrize("name", SCENES)
+def test_queue_lane_state_machine(name, host_scene):
+    """the queue kernels' per-lane state machine (rtb_trace.cuh: LaneTraversal, bounded branch-free pops) gives the
+    reference's hits and performs exactly the in-order global-best traversal's tests"""
+    g = _util.load_golden(name)
+    hs = host_scene(name)
+    rays = _util.box_rays(g["root_box"], g["hit_id"].shape[0], seed=1000)
+    h = _util.devsim_closest_hit_lane(hs, rays, 0)
+    assert np.array_equal(h["id"], g["hit_id"])
+    for k in ("t", "u", "v"):
+        assert np.array_equal(h[k], g["hit_" + k]), k
+    inorder = _util.devsim_closest_hit(hs, rays, rtb.CULL_GLOBAL)
+    assert (h["box_tests"], h["tri_tests"]) == (inorder["box_tests"], inorder["tri_tests"])
+    cam = _util.devsim_closest_hit_lane(hs, _util.camera_rays(_util.golden_camera(g), g["cam_hit_id"].shape[0], seed=2000), 0)
+    assert np.array_equal(cam["id"], g["cam_hit_id"]) and np.array_equal(cam["t"], g["cam_hit_t"])
+
+
 @pytest.mark.parametrize("name", ["s6_1", "soup_10k"])
 def test_reference_cull_counts_equal_twin(name, host_scene):
     """CULL_REFERENCE visits exactly the boxes and triangles the reference's recursion visits"""

@@ -62,8 +62,12 @@ def test_render_counters_equal_cpu_restatement(megakernel, host_scene):
     hs = host_scene("s7_4")
     out = device_scene(hs).render(32, 24, 4, counters=True, megakernel=megakernel)["stats"]
     sim = _util.devsim_render(hs, 32, 24, 4)
-    assert (out["closest_hit_rays"], out["light_pdf_queries"], out["box_tests"], out["tri_tests"]) == (
-        sim["rays"], sim["light_queries"], sim["box_tests"], sim["tri_tests"])
+    assert (out["closest_hit_rays"], out["light_pdf_queries"]) == (sim["rays"], sim["light_queries"])
+    if megakernel:
+        assert (out["box_tests"], out["tri_tests"]) == (sim["box_tests"], sim["tri_tests"])
+    else:   # the ray queue parks leaves: a superset of the in-order traversal's tests
+        assert sim["box_tests"] <= out["box_tests"] <= 1.5 * sim["box_tests"]
+        assert sim["tri_tests"] <= out["tri_tests"] <= 1.5 * sim["tri_tests"]
 
 
 @pytest.mark.parametrize("name,size,spp", [("s7_4", (200, 120), 24), ("sponza_small", (160, 90), 16), ("s6_1", (96, 72), 8)])
