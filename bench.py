@@ -34,6 +34,7 @@ WORKLOADS = {
     "sponza": ("sponza", 1920, 1080, 1024),      # BASELINE.json configs[3], the config the metric is quoted on
     "s7_4": ("s7_4", 1280, 720, 256),            # configs[1]
     "s6_1": ("s6_1", 320, 240, 16),              # configs[0]
+    "soup_10m": ("soup_10m", 3840, 2160, 64),    # configs[4]: 10 M triangles, traversal set > L2 (HBM-bound)
 }
 
 

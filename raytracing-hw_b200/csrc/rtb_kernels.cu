@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(128, MINB) k_closest_hit_queue(const __grid_co
 
 TracePolicy trace_policy() {
     static TracePolicy pol = [] {
-        TracePolicy p = {8, 1, 1};
+        TracePolicy p = {4, 1, 1};   // profiles/r01f_closest_hit_mode_blocks_sweep.jsonl
         if (const char *e = std::getenv("RTB_TRACE_POLICY")) {
             int a = 0, b = 0, c = 0;
             if (std::sscanf(e, "%d,%d,%d", &a, &b, &c) == 3 && a >= 1 && a <= 32 && b >= 1 && c >= 1) p = {a, b, c};
@@ -118,7 +118,7 @@ TracePolicy trace_policy() {
 int trace_mode() {
     static int v = [] {
         int m = kDefaultTraceMode;
-        if (const char *e = std::getenv("RTB_TRACE_MODE")) m = std::atoi(e) != 0 ? 1 : 0;
+        if (const char *e = std::getenv("RTB_TRACE_MODE")) m = std::max(0, std::min(2, std::atoi(e)));
         return m;
     }();
     return v;
@@ -127,7 +127,7 @@ int trace_mode() {
 int persistent_blocks_per_sm() {
     static int v = [] {
         int b = kDefaultTraceBlocks;
-        if (const char *e = std::getenv("RTB_TRACE_BLOCKS")) b = std::max(1, std::min(16, std::atoi(e)));
+        if (const char *e = std::getenv("RTB_TRACE_BLOCKS")) b = std::max(1, std::min(12, std::atoi(e)));
         return b;
     }();
     return v;
@@ -155,12 +155,11 @@ void launch_closest_hit(const DScene &sc, const float *d_rays6, size_t n, int cu
         const unsigned pg = (unsigned) std::min<size_t>((n + block - 1) / block, (size_t) persistent_grid(block, bps));
 #define RTB_LAUNCH_Q(COUNT, MINB, MODE) k_closest_hit_queue<COUNT, MINB, MODE><<<pg, block, 0, stream>>>(sc, d_rays6, (unsigned) n, d_queue_head, d_id, d_t, d_u, d_v, d_inside, d_counters, trace_policy())
 #define RTB_LAUNCH_QM(MODE)                                  \
-        if (d_counters) RTB_LAUNCH_Q(true, 8, MODE);         \
-        else if (bps <= 8) RTB_LAUNCH_Q(false, 8, MODE);     \
+        if (d_counters) RTB_LAUNCH_Q(true, 10, MODE);        \
+        else if (bps <= 9) RTB_LAUNCH_Q(false, 9, MODE);     \
         else if (bps <= 10) RTB_LAUNCH_Q(false, 10, MODE);   \
-        else if (bps <= 12) RTB_LAUNCH_Q(false, 12, MODE);   \
-        else RTB_LAUNCH_Q(false, 16, MODE)
-        if (trace_mode() == 0) { RTB_LAUNCH_QM(0); } else { RTB_LAUNCH_QM(1); }
+        else RTB_LAUNCH_Q(false, 12, MODE)
+        if (trace_mode() == 0) { RTB_LAUNCH_QM(0); } else if (trace_mode() == 1) { RTB_LAUNCH_QM(1); } else { RTB_LAUNCH_QM(2); }
 #undef RTB_LAUNCH_QM
 #undef RTB_LAUNCH_Q
         return;

@@ -51,6 +51,7 @@ struct LaneTraversal {
     int link;
     int tri_i, tri_end;
     float omax, cull;
+    unsigned sgn;           // bit k: direction[k] > 0 (the near-child rule of bvh.cpp:183)
     Ray r;
     Hit best;
 
@@ -64,6 +65,7 @@ struct LaneTraversal {
         tri_i = tri_end = 0;
         omax = 0.f;
         cull = 0.f;
+        sgn = 0u;
         best.t = kFar; best.u = 0.f; best.v = 0.f; best.id = -1;
         for (int k = 0; k < 3; ++k) { r.o[k] = 0.f; r.d[k] = 0.f; r.inv[k] = 0.f; }
     }
@@ -72,14 +74,20 @@ struct LaneTraversal {
     RTB_HD bool wants_pop() const { return link == kPopLink; }
     RTB_HD bool finished() const { return link == kDoneLink; }
 
+    RTB_HD bool nonzero_dir() const { return r.d[0] != 0.f && r.d[1] != 0.f && r.d[2] != 0.f; }
+    // leaf links decode without a branch: kDoneLink / kPopLink carry a zero count, i.e. an empty range; only leaves
+    // with more than 7 triangles (count field 0, an index into the big-leaf table) take the rare branch
     RTB_HD void set_link(const DBvh &b, int l) {
         link = l;
-        if (l < 0 && l != kDoneLink && l != kPopLink) {
-            int first, count;
-            decode_leaf(b, l, first, count);
-            tri_i = first;
-            tri_end = first + count;
+        int count = (l >> 28) & 7;
+        int first = l & 0x0FFFFFFF;
+        if (l < 0 && count == 0 && first < 0x0FFFFFFE) {
+            const int2 bl = ldg(&b.big_leaves[first]);
+            first = bl.x;
+            count = bl.y;
         }
+        tri_i = l < 0 ? first : tri_i;
+        tri_end = l < 0 ? first + count : tri_end;
     }
     RTB_HD void pop(const DBvh &b) {
         const int i1 = sp - 1, i2 = sp >= 2 ? sp - 2 : 0;
@@ -97,18 +105,18 @@ struct LaneTraversal {
         best.t = kFar; best.u = 0.f; best.v = 0.f; best.id = -1;
         omax = ray_omax(r);
         cull = cull_bound(kFar, omax);
+        sgn = (r.d[0] > 0.f ? 1u : 0u) | (r.d[1] > 0.f ? 2u : 0u) | (r.d[2] > 0.f ? 4u : 0u);
         float m0;
         if (COUNT) cnt->box += 1;
         if (box_test_t(r, b.root_box[0], b.root_box[1], b.root_box[2], b.root_box[3], b.root_box[4], b.root_box[5], m0)) set_link(b, b.root_link);
     }
-    template <class C>
+    template <bool NZ, class C>
     RTB_HD void node_compute(const DBvh &b, const float4 na, const float4 nb, const float4 nc, const int4 nd, C *cnt) {
         float ml, mr;
-        const bool hl = box_test_t(r, na.x, na.y, na.z, na.w, nb.x, nb.y, ml);
-        const bool hr = box_test_t(r, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, mr);
+        const bool hl = box_test_t<NZ>(r, na.x, na.y, na.z, na.w, nb.x, nb.y, ml);
+        const bool hr = box_test_t<NZ>(r, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, mr);
         if (COUNT) cnt->box += 2;
-        const float dax = nd.z == 0 ? r.d[0] : (nd.z == 1 ? r.d[1] : r.d[2]);
-        const bool left_first = dax > 0.f;   // bvh.cpp:183
+        const bool left_first = ((sgn >> nd.z) & 1u) != 0u;   // direction[split_dim] > 0 (bvh.cpp:183)
         const int lA = left_first ? nd.x : nd.y, lB = left_first ? nd.y : nd.x;
         const float mA = left_first ? ml : mr, mB = left_first ? mr : ml;
         const bool vA = (left_first ? hl : hr) && !(mA > cull);
@@ -143,7 +151,7 @@ struct LaneTraversal {
         const DNode *np = b.nodes + link;
         const float4 na = ldg(&np->a), nb = ldg(&np->b), nc = ldg(&np->c);
         const int4 nd = ldg(&np->d);
-        node_compute(b, na, nb, nc, nd, cnt);
+        node_compute<false>(b, na, nb, nc, nd, cnt);
     }
     template <class C>
     RTB_HD void tri_step(const DBvh &b, C *cnt) {
@@ -165,10 +173,13 @@ struct LaneTraversal {
 // no ray (a finished slot of the wavefront integrator); Emit(tag, ray, hit) stores the result of the entry's ray.
 //
 // MODE 0 (voted phases): each warp iteration runs ONE phase chosen by vote (refill / node / triangle).
-// MODE 1 (unified step): each warp iteration serves EVERY lane: one fetch stage in which a lane loads its node
+// MODE >= 1 (unified step): each step serves EVERY lane: one fetch stage in which a lane loads its node
 //   (4 x LDG.128) or its triangle (3 x LDG.128) through the same instructions, then the node code for the lanes
 //   holding a node and the triangle code for the lanes holding a triangle.  Half the iterations per ray of MODE 0
-//   (a lane never waits for its phase to win a vote), so half the exposed memory latencies; see DESIGN.md.
+//   (a lane never waits for its phase to win a vote), so half the exposed memory latencies; MODE steps are taken
+//   between two refill votes.  See DESIGN.md for the ncu evidence and for what was tried and dropped (parked leaves,
+//   batching the triangle code, a separate instantiation for rays without zero direction components: each cost more
+//   in registers -- occupancy -- than it saved in instructions).
 template <bool COUNT, int MODE, class Fetch, class Emit>
 __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsigned *queue_head, Fetch fetch, Emit emit, QueueCounters *cnt, const TracePolicy pol) {
     const unsigned FULL = 0xffffffffu;
@@ -208,9 +219,9 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
             }
             continue;
         }
-        if (L.wants_pop()) L.pop(b);
-        const bool doN = L.wants_node(), doL = L.wants_tri();
         if (MODE == 0) {
+            if (L.wants_pop()) L.pop(b);
+            const bool doN = L.wants_node(), doL = L.wants_tri();
             const int cN = __popc(__ballot_sync(FULL, doN)), cL = __popc(__ballot_sync(FULL, doL));
             if (cN * pol.w_node >= cL * pol.w_leaf) {
                 if (doN) L.node_step(b, cnt);
@@ -218,18 +229,24 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
                 if (doL) L.tri_step(b, cnt);
             }
         } else {
-            // one fetch stage for both kinds of record
-            const float4 *p = doN ? reinterpret_cast<const float4 *>(b.nodes + L.link) : (b.tris + (size_t) L.tri_i * 3);
-            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a, c = a;
-            int4 d = make_int4(0, 0, 0, 0);
-            if (doN || doL) {
-                a = __ldg(p);
-                bb = __ldg(p + 1);
-                c = __ldg(p + 2);
+#pragma unroll
+            for (int step = 0; step < MODE; ++step) {
+                if (L.wants_pop()) L.pop(b);
+                const bool doN = L.wants_node();
+                const bool doL = L.wants_tri();
+                // one fetch stage for both kinds of record
+                const float4 *p = doN ? reinterpret_cast<const float4 *>(b.nodes + L.link) : (b.tris + (size_t) L.tri_i * 3);
+                float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a, c = a;
+                int4 d = make_int4(0, 0, 0, 0);
+                if (doN || doL) {
+                    a = __ldg(p);
+                    bb = __ldg(p + 1);
+                    c = __ldg(p + 2);
+                }
+                if (doN) d = __ldg(reinterpret_cast<const int4 *>(p + 3));
+                if (doN) L.template node_compute<false>(b, a, bb, c, d, cnt);
+                if (doL) L.tri_compute(b, a, bb, c, cnt);
             }
-            if (doN) d = __ldg(reinterpret_cast<const int4 *>(p + 3));
-            if (doN) L.node_compute(b, a, bb, c, d, cnt);
-            if (doL) L.tri_compute(b, a, bb, c, cnt);
         }
     }
 }

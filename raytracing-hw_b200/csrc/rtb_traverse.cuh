@@ -74,15 +74,18 @@ RTB_HD bool box_test_sq(const Ray &r, float mnx, float mny, float mnz, float mxx
 
 // AABB::intersect, predicated, without the entry distance.  hit <=> the reference returns a value; tmax = the ray
 // parameter of the candidate plane (primitive.cpp:176-190), -1 when the origin is inside the box.
+// NZ: the caller guarantees that no component of the direction is zero (the `dir[i] != 0.` guards of primitive.cpp:178
+// are then always true and are not evaluated).
+template <bool NZ = false>
 RTB_HD bool box_test_t(const Ray &r, float mnx, float mny, float mnz, float mxx, float mxy, float mxz, float &tmax) {
     const bool lo0 = r.o[0] < mnx, hi0 = r.o[0] > mxx;
     const bool lo1 = r.o[1] < mny, hi1 = r.o[1] > mxy;
     const bool lo2 = r.o[2] < mnz, hi2 = r.o[2] > mxz;
     const float pl0 = lo0 ? mnx : mxx, pl1 = lo1 ? mny : mxy, pl2 = lo2 ? mnz : mxz;
     const bool out0 = lo0 || hi0, out1 = lo1 || hi1, out2 = lo2 || hi2;   // quadrant != Mid
-    const float t0 = (out0 && r.d[0] != 0.f) ? (pl0 - r.o[0]) * r.inv[0] : -1.f;
-    const float t1 = (out1 && r.d[1] != 0.f) ? (pl1 - r.o[1]) * r.inv[1] : -1.f;
-    const float t2 = (out2 && r.d[2] != 0.f) ? (pl2 - r.o[2]) * r.inv[2] : -1.f;
+    const float t0 = (out0 && (NZ || r.d[0] != 0.f)) ? (pl0 - r.o[0]) * r.inv[0] : -1.f;
+    const float t1 = (out1 && (NZ || r.d[1] != 0.f)) ? (pl1 - r.o[1]) * r.inv[1] : -1.f;
+    const float t2 = (out2 && (NZ || r.d[2] != 0.f)) ? (pl2 - r.o[2]) * r.inv[2] : -1.f;
     const bool w1 = t0 < t1;                 // whichPlane = 1 (unless 2 wins)
     float tm = w1 ? t1 : t0;
     const bool w2 = tm < t2;                 // whichPlane = 2

@@ -14,6 +14,7 @@
 #include "rtb_wavefront.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 #include <vector>
 #include "rtb_trace.cuh"
 
@@ -21,6 +22,7 @@ namespace rtb {
 
 namespace {
 constexpr int kShadeBlock = 128;
+constexpr int kDefaultShadeBlocks = 6;   // CTAs per SM the shade kernel is compiled for (RTB_SHADE_BLOCKS: 5, 6, 8)
 constexpr int kCompactBlock = 1024;
 
 __global__ void __launch_bounds__(256) k_wf_init(const __grid_constant__ DScene sc, const RenderLaunch p, const WfState w,
@@ -69,8 +71,8 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(const __grid_constant__ 
     }
 }
 
-template <bool COUNT>
-__global__ void __launch_bounds__(kShadeBlock) k_wf_shade(const __grid_constant__ DScene sc, const RenderLaunch p, const WfState w,
+template <bool COUNT, int MINB>
+__global__ void __launch_bounds__(kShadeBlock, MINB) k_wf_shade(const __grid_constant__ DScene sc, const RenderLaunch p, const WfState w,
                                                           unsigned *__restrict__ list, const unsigned *__restrict__ n_list,
                                                           unsigned *__restrict__ queue_head) {
     const unsigned n = *n_list;
@@ -244,6 +246,11 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
     const unsigned trace_grid = (unsigned) std::min<size_t>(((size_t) n_slots + 127) / 128, (size_t) persistent_grid(128, bps));
     const TracePolicy pol = trace_policy();
     const int mode = trace_mode();
+    static const int shade_bps = [] {
+        int v = kDefaultShadeBlocks;
+        if (const char *e = std::getenv("RTB_SHADE_BLOCKS")) v = std::atoi(e);
+        return v;
+    }();
     const unsigned shade_grid = (unsigned) std::min<size_t>(((size_t) n_slots + kShadeBlock - 1) / kShadeBlock, (size_t) persistent_grid(kShadeBlock, 16));
     const long long iterations = (long long) p.samples * sc.ray_depth;
     const int period = 16;   // iterations between compactions
@@ -262,17 +269,18 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
         mark();
 #define RTB_LAUNCH_T(COUNT, MINB, MODE) k_wf_trace<COUNT, MINB, MODE><<<trace_grid, 128, 0, stream>>>(sc, w, lists[cur], n_list[cur], queue_head, p.d_counters, pol)
 #define RTB_LAUNCH_TM(MODE)                                      \
-        if (p.count_tests) RTB_LAUNCH_T(true, 8, MODE);          \
-        else if (bps <= 8) RTB_LAUNCH_T(false, 8, MODE);         \
+        if (p.count_tests) RTB_LAUNCH_T(true, 10, MODE);         \
+        else if (bps <= 9) RTB_LAUNCH_T(false, 9, MODE);         \
         else if (bps <= 10) RTB_LAUNCH_T(false, 10, MODE);       \
-        else if (bps <= 12) RTB_LAUNCH_T(false, 12, MODE);       \
-        else RTB_LAUNCH_T(false, 16, MODE)
-        if (mode == 0) { RTB_LAUNCH_TM(0); } else { RTB_LAUNCH_TM(1); }
+        else RTB_LAUNCH_T(false, 12, MODE)
+        if (mode == 0) { RTB_LAUNCH_TM(0); } else if (mode == 1) { RTB_LAUNCH_TM(1); } else { RTB_LAUNCH_TM(2); }
 #undef RTB_LAUNCH_TM
 #undef RTB_LAUNCH_T
         mark();
-        if (p.count_tests) k_wf_shade<true><<<shade_grid, kShadeBlock, 0, stream>>>(sc, p, w, lists[cur], n_list[cur], queue_head);
-        else k_wf_shade<false><<<shade_grid, kShadeBlock, 0, stream>>>(sc, p, w, lists[cur], n_list[cur], queue_head);
+        if (p.count_tests) k_wf_shade<true, 5><<<shade_grid, kShadeBlock, 0, stream>>>(sc, p, w, lists[cur], n_list[cur], queue_head);
+        else if (shade_bps <= 5) k_wf_shade<false, 5><<<shade_grid, kShadeBlock, 0, stream>>>(sc, p, w, lists[cur], n_list[cur], queue_head);
+        else if (shade_bps <= 6) k_wf_shade<false, 6><<<shade_grid, kShadeBlock, 0, stream>>>(sc, p, w, lists[cur], n_list[cur], queue_head);
+        else k_wf_shade<false, 8><<<shade_grid, kShadeBlock, 0, stream>>>(sc, p, w, lists[cur], n_list[cur], queue_head);
         nl += 2;
         if ((it + 1) % period == 0 && it + 1 < iterations) compact();
     }
