@@ -43,6 +43,8 @@ struct rtb_scene {
     void *wf_state = nullptr;
     size_t wf_bytes = 0;
     unsigned long long launches = 0;   // kernels launched by rtb_render_device calls on this scene
+    rtb::WfStreams wf_streams;               // slot-group streams of the wavefront integrator
+    bool wf_streams_ok = false;
     std::vector<cudaEvent_t> stage_events;   // RTB_RENDER_STAGE_TIMES: events of the last such frame
     bool stage_events_valid = false;
     ~rtb_scene() {
@@ -51,6 +53,11 @@ struct rtb_scene {
         if (stage) cudaFree(stage);
         if (wf_state) cudaFree(wf_state);
         for (auto &e : stage_events) cudaEventDestroy(e);
+        if (wf_streams_ok) {
+            for (auto &s : wf_streams.stream) cudaStreamDestroy(s);
+            for (auto &e : wf_streams.join) cudaEventDestroy(e);
+            cudaEventDestroy(wf_streams.fork);
+        }
         if (queue_heads) cudaFree(queue_heads);
         for (auto &s : streams) if (s) cudaStreamDestroy(s);
         for (auto &e : ev) if (e) cudaEventDestroy(e);
@@ -314,8 +321,14 @@ int rtb_render_device(rtb_scene *scene, const rtb_render_params *p, float *d_acc
             scene->wf_bytes = need;
         }
         const bool timed = (p->flags & RTB_RENDER_STAGE_TIMES) != 0;
+        if (!scene->wf_streams_ok) {
+            for (auto &s : scene->wf_streams.stream) RTB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+            for (auto &e : scene->wf_streams.join) RTB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            RTB_CUDA(cudaEventCreateWithFlags(&scene->wf_streams.fork, cudaEventDisableTiming));
+            scene->wf_streams_ok = true;
+        }
         rtb::launch_render_wavefront(scene->d, L, scene->wf_state, (cudaStream_t) stream, &scene->launches,
-                                     timed ? &scene->stage_events : nullptr);
+                                     timed ? &scene->stage_events : nullptr, &scene->wf_streams);
         scene->stage_events_valid = timed;
     }
     RTB_CUDA(cudaGetLastError());

@@ -32,8 +32,13 @@ void launch_render(const DScene &sc, const RenderLaunch &p, cudaStream_t stream)
 unsigned wf_slots(const RenderLaunch &p);
 size_t wf_alloc_bytes(unsigned n_slots, int depth_cap);
 // stage_events (may be null): filled with events bracketing every k_wf_trace launch, see rtb_scene_stage_ms()
+constexpr int kWfMaxGroups = 2;
+struct WfStreams {   // owned by the scene: one stream per slot group + fork / join events (null: one group, caller's stream)
+    cudaStream_t stream[kWfMaxGroups];
+    cudaEvent_t fork, join[kWfMaxGroups];
+};
 void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *state, cudaStream_t stream, unsigned long long *launches,
-                             std::vector<cudaEvent_t> *stage_events);
+                             std::vector<cudaEvent_t> *stage_events, const WfStreams *aux);
 void launch_resolve(const float *d_accum, size_t n_pixels, int samples, uint8_t *d_rgb8, cudaStream_t stream);
 
 }  // namespace rtb

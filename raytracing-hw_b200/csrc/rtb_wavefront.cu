@@ -25,14 +25,16 @@ constexpr int kShadeBlock = 128;
 constexpr int kDefaultShadeBlocks = 6;   // CTAs per SM the shade kernel is compiled for (RTB_SHADE_BLOCKS: 5, 6, 8)
 constexpr int kCompactBlock = 1024;
 
-__global__ void __launch_bounds__(256) k_wf_init(const __grid_constant__ DScene sc, const RenderLaunch p, const WfState w,
-                                                 unsigned *__restrict__ list, unsigned *__restrict__ n_list, unsigned *__restrict__ queue_head) {
-    const unsigned slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot == 0) {
-        *n_list = w.n_slots;
+// slots [slot_begin, slot_begin + count) of one slot group; list / n_list / queue_head are the group's own
+__global__ void __launch_bounds__(256) k_wf_init(const __grid_constant__ DScene sc, const RenderLaunch p, const WfState w, unsigned slot_begin,
+                                                 unsigned count, unsigned *__restrict__ list, unsigned *__restrict__ n_list,
+                                                 unsigned *__restrict__ queue_head) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) {
+        *n_list = count;
         *queue_head = 0u;
     }
-    if (slot < w.n_slots) list[slot] = wf_init_slot(sc, p, w, slot);
+    if (i < count) list[i] = wf_init_slot(sc, p, w, slot_begin + i);
 }
 
 template <bool COUNT, int MINB, int MODE>
@@ -179,11 +181,11 @@ __global__ void __launch_bounds__(kCompactBlock) k_wf_scatter(const unsigned *__
 
 size_t wf_state_bytes(unsigned n_slots, int depth_cap) {
     const size_t per_slot = 16 + 8 + 16 + 16 + 16 + (size_t) depth_cap * (16 + 16 + 4) + 2 * 4;
-    const size_t blocks = ((size_t) n_slots + kCompactBlock - 1) / kCompactBlock;
+    const size_t blocks = ((size_t) n_slots + kCompactBlock - 1) / kCompactBlock + kWfMaxGroups;
     return per_slot * n_slots + blocks * 4 + 4096;
 }
 
-// Carves the state arrays out of one allocation (`base`, wf_state_bytes() bytes, 256-byte aligned).
+// Carves the state arrays out of one allocation (`base`, wf_alloc_bytes() bytes, 256-byte aligned).
 static void wf_carve(char *base, unsigned n_slots, int depth_cap, WfState &w, unsigned *lists[2], unsigned **block_counts, unsigned **scalars) {
     size_t off = 0;
     auto take = [&](size_t bytes) {
@@ -203,8 +205,8 @@ static void wf_carve(char *base, unsigned n_slots, int depth_cap, WfState &w, un
     w.stk_a = (float *) take((size_t) n_slots * 4 * depth_cap);
     lists[0] = (unsigned *) take((size_t) n_slots * 4);
     lists[1] = (unsigned *) take((size_t) n_slots * 4);
-    *block_counts = (unsigned *) take((((size_t) n_slots + kCompactBlock - 1) / kCompactBlock) * 4);
-    *scalars = (unsigned *) take(64);
+    *block_counts = (unsigned *) take((((size_t) n_slots + kCompactBlock - 1) / kCompactBlock + kWfMaxGroups) * 4);
+    *scalars = (unsigned *) take(256);
 }
 
 size_t wf_alloc_bytes(unsigned n_slots, int depth_cap) {
@@ -217,33 +219,83 @@ unsigned wf_slots(const RenderLaunch &p) {
     return (unsigned) (tiles * 32);
 }
 
+int wf_groups() {
+    static const int v = [] {
+        int g = kWfMaxGroups;
+        if (const char *e = std::getenv("RTB_WF_GROUPS")) g = std::max(1, std::min(kWfMaxGroups, std::atoi(e)));
+        return g;
+    }();
+    return v;
+}
+
+// Slot groups.  The slots are cut into up to kWfMaxGroups contiguous groups, each with its own active list, queue
+// cursor and stream (`aux`).  Inside a group the kernels of an iteration are ordered (trace -> shade); the groups are
+// independent, so the tail of one group's queue kernel (lanes running dry one by one) and its latency-bound shade
+// kernel overlap the other group's ALU-bound queue kernel.  With stage timing on, one group on the caller's stream:
+// a kernel's duration is only defined when it runs alone.
 void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *state, cudaStream_t stream, unsigned long long *launches,
-                             std::vector<cudaEvent_t> *stage_events) {
+                             std::vector<cudaEvent_t> *stage_events, const WfStreams *aux) {
     if (p.local_rows <= 0 || p.width <= 0 || p.samples <= 0) return;
     const unsigned n_slots = wf_slots(p);
     const int depth_cap = std::max(1, sc.ray_depth - 1);
     WfState w;
     unsigned *lists[2], *block_counts, *scalars;
     wf_carve((char *) state, n_slots, depth_cap, w, lists, &block_counts, &scalars);
-    unsigned *n_list[2] = {scalars, scalars + 1};
-    unsigned *queue_head = scalars + 2;
-    const unsigned n_blocks = (n_slots + kCompactBlock - 1) / kCompactBlock;
     unsigned long long nl = 0;
 
-    int cur = 0;
-    auto compact = [&]() {
-        k_wf_count<<<n_blocks, kCompactBlock, 0, stream>>>(lists[cur], n_list[cur], block_counts);
-        k_wf_scan<<<1, 1024, 0, stream>>>(block_counts, n_blocks, n_list[cur ^ 1]);
-        k_wf_scatter<<<n_blocks, kCompactBlock, 0, stream>>>(lists[cur], n_list[cur], block_counts, lists[cur ^ 1]);
-        cur ^= 1;
+    // a group needs enough slots to fill the persistent queue kernel a few times over
+    int G = (stage_events || !aux) ? 1 : wf_groups();
+    while (G > 1 && n_slots / (unsigned) G < 32u * 1024u) --G;
+    struct Group {
+        unsigned begin, count, n_blocks, block_off;
+        unsigned *lists[2], *n_list[2], *queue_head;
+        int cur;
+        cudaStream_t st;
+        unsigned trace_grid, shade_grid;
+    } grp[kWfMaxGroups];
+    const int bps = persistent_blocks_per_sm();
+    {
+        const unsigned tiles = n_slots / 32u;
+        unsigned t0 = 0, boff = 0;
+        for (int g = 0; g < G; ++g) {
+            const unsigned t1 = (unsigned) ((unsigned long long) tiles * (g + 1) / G);
+            Group &q = grp[g];
+            q.begin = t0 * 32u;
+            q.count = (t1 - t0) * 32u;
+            q.n_blocks = (q.count + kCompactBlock - 1) / kCompactBlock;
+            q.block_off = boff;
+            boff += q.n_blocks;
+            q.lists[0] = lists[0] + q.begin;
+            q.lists[1] = lists[1] + q.begin;
+            q.n_list[0] = scalars + 4 * g;
+            q.n_list[1] = scalars + 4 * g + 1;
+            q.queue_head = scalars + 4 * g + 2;
+            q.cur = 0;
+            q.st = G > 1 ? aux->stream[g] : stream;
+            // the groups share the SMs: each gets its share of the persistent grid
+            q.trace_grid = (unsigned) std::min<size_t>(((size_t) q.count + 127) / 128, (size_t) persistent_grid(128, bps));
+            q.shade_grid = (unsigned) std::min<size_t>(((size_t) q.count + kShadeBlock - 1) / kShadeBlock, (size_t) persistent_grid(kShadeBlock, 16));
+            t0 = t1;
+        }
+    }
+    if (G > 1) {   // fork: the groups' streams start after everything already queued on the caller's stream
+        cudaEventRecord(aux->fork, stream);
+        for (int g = 0; g < G; ++g) cudaStreamWaitEvent(grp[g].st, aux->fork, 0);
+    }
+    auto compact = [&](Group &q) {
+        unsigned *bc = block_counts + q.block_off;
+        k_wf_count<<<q.n_blocks, kCompactBlock, 0, q.st>>>(q.lists[q.cur], q.n_list[q.cur], bc);
+        k_wf_scan<<<1, 1024, 0, q.st>>>(bc, q.n_blocks, q.n_list[q.cur ^ 1]);
+        k_wf_scatter<<<q.n_blocks, kCompactBlock, 0, q.st>>>(q.lists[q.cur], q.n_list[q.cur], bc, q.lists[q.cur ^ 1]);
+        q.cur ^= 1;
         nl += 3;
     };
-
-    k_wf_init<<<(n_slots + 255) / 256, 256, 0, stream>>>(sc, p, w, lists[0], n_list[0], queue_head);
-    ++nl;
-    compact();   // drops the slots outside the canvas
-    const int bps = persistent_blocks_per_sm();
-    const unsigned trace_grid = (unsigned) std::min<size_t>(((size_t) n_slots + 127) / 128, (size_t) persistent_grid(128, bps));
+    for (int g = 0; g < G; ++g) {
+        Group &q = grp[g];
+        k_wf_init<<<(q.count + 255) / 256, 256, 0, q.st>>>(sc, p, w, q.begin, q.count, q.lists[0], q.n_list[0], q.queue_head);
+        ++nl;
+        compact(q);   // drops the slots outside the canvas
+    }
     const TracePolicy pol = trace_policy();
     const int mode = trace_mode();
     static const int shade_bps = [] {
@@ -251,7 +303,6 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
         if (const char *e = std::getenv("RTB_SHADE_BLOCKS")) v = std::atoi(e);
         return v;
     }();
-    const unsigned shade_grid = (unsigned) std::min<size_t>(((size_t) n_slots + kShadeBlock - 1) / kShadeBlock, (size_t) persistent_grid(kShadeBlock, 16));
     const long long iterations = (long long) p.samples * sc.ray_depth;
     const int period = 16;   // iterations between compactions
     // optional stage timing: events[2*it], events[2*it+1] bracket iteration it's k_wf_trace; events[2*iterations] ends the frame
@@ -266,28 +317,37 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
         cudaEventRecord((*stage_events)[ev_i++], stream);
     };
     for (long long it = 0; it < iterations; ++it) {
-        mark();
-#define RTB_LAUNCH_T(COUNT, MINB, MODE) k_wf_trace<COUNT, MINB, MODE><<<trace_grid, 128, 0, stream>>>(sc, w, lists[cur], n_list[cur], queue_head, p.d_counters, pol)
-#define RTB_LAUNCH_TM(MODE)                                      \
-        if (p.count_tests) RTB_LAUNCH_T(true, 10, MODE);         \
-        else if (bps <= 9) RTB_LAUNCH_T(false, 9, MODE);         \
-        else if (bps <= 10) RTB_LAUNCH_T(false, 10, MODE);       \
-        else RTB_LAUNCH_T(false, 12, MODE)
-        if (mode == 0) { RTB_LAUNCH_TM(0); } else if (mode == 1) { RTB_LAUNCH_TM(1); } else { RTB_LAUNCH_TM(2); }
+        for (int g = 0; g < G; ++g) {
+            Group &q = grp[g];
+            unsigned *list = q.lists[q.cur], *n_list = q.n_list[q.cur];
+            mark();
+#define RTB_LAUNCH_T(COUNT, MINB, MODE) k_wf_trace<COUNT, MINB, MODE><<<q.trace_grid, 128, 0, q.st>>>(sc, w, list, n_list, q.queue_head, p.d_counters, pol)
+#define RTB_LAUNCH_TM(MODE)                                          \
+            if (p.count_tests) RTB_LAUNCH_T(true, 10, MODE);         \
+            else if (bps <= 9) RTB_LAUNCH_T(false, 9, MODE);         \
+            else if (bps <= 10) RTB_LAUNCH_T(false, 10, MODE);       \
+            else RTB_LAUNCH_T(false, 12, MODE)
+            if (mode == 0) { RTB_LAUNCH_TM(0); } else if (mode == 1) { RTB_LAUNCH_TM(1); } else { RTB_LAUNCH_TM(2); }
 #undef RTB_LAUNCH_TM
 #undef RTB_LAUNCH_T
-        mark();
-        if (p.count_tests) k_wf_shade<true, 5><<<shade_grid, kShadeBlock, 0, stream>>>(sc, p, w, lists[cur], n_list[cur], queue_head);
-        else if (shade_bps <= 5) k_wf_shade<false, 5><<<shade_grid, kShadeBlock, 0, stream>>>(sc, p, w, lists[cur], n_list[cur], queue_head);
-        else if (shade_bps <= 6) k_wf_shade<false, 6><<<shade_grid, kShadeBlock, 0, stream>>>(sc, p, w, lists[cur], n_list[cur], queue_head);
-        else k_wf_shade<false, 8><<<shade_grid, kShadeBlock, 0, stream>>>(sc, p, w, lists[cur], n_list[cur], queue_head);
-        nl += 2;
-        if ((it + 1) % period == 0 && it + 1 < iterations) compact();
+            mark();
+            if (p.count_tests) k_wf_shade<true, 5><<<q.shade_grid, kShadeBlock, 0, q.st>>>(sc, p, w, list, n_list, q.queue_head);
+            else if (shade_bps <= 5) k_wf_shade<false, 5><<<q.shade_grid, kShadeBlock, 0, q.st>>>(sc, p, w, list, n_list, q.queue_head);
+            else if (shade_bps <= 6) k_wf_shade<false, 6><<<q.shade_grid, kShadeBlock, 0, q.st>>>(sc, p, w, list, n_list, q.queue_head);
+            else k_wf_shade<false, 8><<<q.shade_grid, kShadeBlock, 0, q.st>>>(sc, p, w, list, n_list, q.queue_head);
+            nl += 2;
+            if ((it + 1) % period == 0 && it + 1 < iterations) compact(q);
+        }
     }
     mark();
+    if (G > 1) {   // join
+        for (int g = 0; g < G; ++g) {
+            cudaEventRecord(aux->join[g], grp[g].st);
+            cudaStreamWaitEvent(stream, aux->join[g], 0);
+        }
+    }
     if (stage_events) stage_events->resize(ev_i);   // (events beyond ev_i were created by an earlier, longer frame)
     if (launches) *launches += nl;
 }
-
 
 }  // namespace rtb
