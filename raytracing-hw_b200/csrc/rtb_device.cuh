@@ -123,6 +123,16 @@ RTB_HD void make_ray(Ray &r, float ox, float oy, float oz, float dx, float dy, f
     r.d[0] = dx * mod; r.d[1] = dy * mod; r.d[2] = dz * mod;
     r.inv[0] = 1.f / r.d[0]; r.inv[1] = 1.f / r.d[1]; r.inv[2] = 1.f / r.d[2];
 }
+// same without inv_direction, for queries that are known not to run a ray/box test
+RTB_HD void make_ray_no_inv(Ray &r, float ox, float oy, float oz, float dx, float dy, float dz) {
+    float mod = dx * dx;
+    mod = mod + dy * dy;
+    mod = mod + dz * dz;
+    mod = 1.f / sqrtf(mod);
+    r.o[0] = ox; r.o[1] = oy; r.o[2] = oz;
+    r.d[0] = dx * mod; r.d[1] = dy * mod; r.d[2] = dz * mod;
+    r.inv[0] = 0.f; r.inv[1] = 0.f; r.inv[2] = 0.f;
+}
 
 // AABB::intersect (primitive.cpp:146-208).  Returns hit?; dist = entry distance (0 when the origin is inside).
 RTB_HD bool box_test(const Ray &r, float mnx, float mny, float mnz, float mxx, float mxy, float mxz, float &dist) {

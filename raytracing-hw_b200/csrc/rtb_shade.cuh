@@ -217,7 +217,10 @@ RTB_HD V3 sample_light(const DScene &sc, V3 point, Rng &g) {
 template <bool COUNT>
 RTB_HD float pdf_lights(const DScene &sc, V3 point, V3 dir, Counters *cnt) {
     Ray r;
-    make_ray(r, point.x, point.y, point.z, dir.x, dir.y, dir.z);   // Ray{point, direction} re-normalises
+    // Ray{point, direction} re-normalises; inv_direction only feeds ray/box tests, and a light BVH that is a single
+    // leaf (two light triangles in Sponza, practice7_*) runs none (intersectAll does not test the root box)
+    if (sc.light_bvh.root_link >= 0) make_ray(r, point.x, point.y, point.z, dir.x, dir.y, dir.z);
+    else make_ray_no_inv(r, point.x, point.y, point.z, dir.x, dir.y, dir.z);
     float prob = 0.f;
     const float *inv_area = sc.light_inv_area;
     all_hits<COUNT>(sc.light_bvh, r, cnt, [&](int li, float t, const float4 &q2) {

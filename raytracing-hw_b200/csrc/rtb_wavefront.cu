@@ -24,6 +24,7 @@ namespace {
 constexpr int kShadeBlock = 128;
 constexpr int kDefaultShadeBlocks = 6;   // CTAs per SM the shade kernel is compiled for (RTB_SHADE_BLOCKS: 5, 6, 8)
 constexpr int kCompactBlock = 1024;
+constexpr int kDefaultRaysPerLane = 1;   // k_wf_trace keeps ceil(active / (128 * this)) CTAs (RTB_TRACE_RPL)
 
 // slots [slot_begin, slot_begin + count) of one slot group; list / n_list / queue_head are the group's own
 __global__ void __launch_bounds__(256) k_wf_init(const __grid_constant__ DScene sc, const RenderLaunch p, const WfState w, unsigned slot_begin,
@@ -40,9 +41,12 @@ __global__ void __launch_bounds__(256) k_wf_init(const __grid_constant__ DScene 
 template <bool COUNT, int MINB, int MODE>
 __global__ void __launch_bounds__(128, MINB) k_wf_trace(const __grid_constant__ DScene sc, const WfState w, const unsigned *__restrict__ list,
                                                   const unsigned *__restrict__ n_list, unsigned *__restrict__ queue_head,
-                                                  unsigned long long *__restrict__ counters, const TracePolicy pol) {
+                                                  unsigned long long *__restrict__ counters, const TracePolicy pol,
+                                                  const unsigned rays_per_lane) {
     const unsigned n = *n_list;
-    if (n == 0) return;
+    // the grid was sized on the host for the list's capacity; when few slots are still active, the surplus CTAs leave
+    // at once so that every remaining lane still pulls several rays from the queue (dynamic balance needs that)
+    if (n == 0 || (blockIdx.x > 0 && blockIdx.x * (128u * rays_per_lane) >= n)) return;
     QueueCounters cnt = {0ull, 0ull, 0ull};
     trace_persistent<COUNT, MODE>(
         sc.bvh, n, queue_head,
@@ -303,6 +307,11 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
         if (const char *e = std::getenv("RTB_SHADE_BLOCKS")) v = std::atoi(e);
         return v;
     }();
+    static const unsigned rays_per_lane = [] {
+        int v = kDefaultRaysPerLane;
+        if (const char *e = std::getenv("RTB_TRACE_RPL")) v = std::max(1, std::atoi(e));
+        return (unsigned) v;
+    }();
     const long long iterations = (long long) p.samples * sc.ray_depth;
     const int period = 16;   // iterations between compactions
     // optional stage timing: events[2*it], events[2*it+1] bracket iteration it's k_wf_trace; events[2*iterations] ends the frame
@@ -321,7 +330,7 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
             Group &q = grp[g];
             unsigned *list = q.lists[q.cur], *n_list = q.n_list[q.cur];
             mark();
-#define RTB_LAUNCH_T(COUNT, MINB, MODE) k_wf_trace<COUNT, MINB, MODE><<<q.trace_grid, 128, 0, q.st>>>(sc, w, list, n_list, q.queue_head, p.d_counters, pol)
+#define RTB_LAUNCH_T(COUNT, MINB, MODE) k_wf_trace<COUNT, MINB, MODE><<<q.trace_grid, 128, 0, q.st>>>(sc, w, list, n_list, q.queue_head, p.d_counters, pol, rays_per_lane)
 #define RTB_LAUNCH_TM(MODE)                                          \
             if (p.count_tests) RTB_LAUNCH_T(true, 10, MODE);         \
             else if (bps <= 9) RTB_LAUNCH_T(false, 9, MODE);         \
