@@ -110,7 +110,8 @@ def cpu_reference_render(scene_path, w, h, s, threads=0):
     if not ref_oracle.available():
         return None
     rs = ref_oracle.RefScene.from_gltf(scene_path, w, h, s)
-    _, sec = rs.render(threads=threads)
+    # all host threads, explicitly: torchrun exports OMP_NUM_THREADS=1 to its workers
+    _, sec = rs.render(threads=threads or (os.cpu_count() or 1))
     rs.close()
     return sec
 
