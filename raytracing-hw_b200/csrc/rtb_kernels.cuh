@@ -32,7 +32,7 @@ void launch_render(const DScene &sc, const RenderLaunch &p, cudaStream_t stream)
 unsigned wf_slots(const RenderLaunch &p);
 size_t wf_alloc_bytes(unsigned n_slots, int depth_cap);
 // stage_events (may be null): filled with events bracketing every k_wf_trace launch, see rtb_scene_stage_ms()
-constexpr int kWfMaxGroups = 2;
+constexpr int kWfMaxGroups = 8;
 struct WfStreams {   // owned by the scene: one stream per slot group + fork / join events (null: one group, caller's stream)
     cudaStream_t stream[kWfMaxGroups];
     cudaEvent_t fork, join[kWfMaxGroups];

@@ -223,13 +223,18 @@ unsigned wf_slots(const RenderLaunch &p) {
     return (unsigned) (tiles * 32);
 }
 
-int wf_groups() {
-    static const int v = [] {
-        int g = kWfMaxGroups;
+// Measured on one B200 (Sponza stand-in, 64 spp; gpurun_out of run 14): 2.07 M slots -> 1 or 2 groups are best (4: -5 %,
+// 8: -13 %); 0.26 M slots (one GPU's share of a 1080p frame on 8 GPUs) -> 144 / 128 / 117 / 112 ms with 1 / 2 / 4 / 8
+// groups.  Default: as many groups as it takes to bring a group down to ~0.26 M slots.
+int wf_groups(unsigned n_slots) {
+    static const int forced = [] {
+        int g = 0;
         if (const char *e = std::getenv("RTB_WF_GROUPS")) g = std::max(1, std::min(kWfMaxGroups, std::atoi(e)));
         return g;
     }();
-    return v;
+    if (forced) return forced;
+    const unsigned g = ((2u << 20) + n_slots / 2) / std::max(1u, n_slots);
+    return (int) std::max(1u, std::min((unsigned) kWfMaxGroups, g));
 }
 
 // Slot groups.  The slots are cut into up to kWfMaxGroups contiguous groups, each with its own active list, queue
@@ -248,7 +253,7 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
     unsigned long long nl = 0;
 
     // a group needs enough slots to fill the persistent queue kernel a few times over
-    int G = (stage_events || !aux) ? 1 : wf_groups();
+    int G = (stage_events || !aux) ? 1 : wf_groups(n_slots);
     while (G > 1 && n_slots / (unsigned) G < 32u * 1024u) --G;
     struct Group {
         unsigned begin, count, n_blocks, block_off;
