@@ -159,6 +159,75 @@ struct LaneTraversal {
         const float4 q0 = ldg(tp), q1 = ldg(tp + 1), q2 = ldg(tp + 2);
         tri_compute(b, q0, q1, q2, cnt);
     }
+    // ---- form 3 (MODE 3 of trace_persistent): ONE pop site and ONE leaf-decode site per step, both at the top of the
+    // step where the lanes are converged.  node_compute3 / tri_compute3 only leave `link` behind (an internal node, a
+    // not yet decoded leaf, or kPopLink); pre3 pops for the lanes that asked for it and decodes fresh leaves.  In the
+    // first form these two pieces were inlined at three places each and ran at 3 to 6 active lanes: 20 % of all
+    // issued instructions (profiles/r01h_k_wf_trace_lines.txt).  Same visits, same arithmetic, same results.
+    // A leaf link is "fresh" while tri_i == tri_end (node lanes and popping lanes never hold pending triangles).
+    RTB_HD void pre3(const DBvh &b) {
+        if (link == kPopLink) {
+            const int i1 = sp - 1, i2 = sp >= 2 ? sp - 2 : 0;
+            const int l1 = s_link[i1], l2 = s_link[i2];
+            const float m1 = s_m[i1], m2 = s_m[i2];
+            const bool k1 = !(m1 > cull), k2 = !(m2 > cull);
+            link = k1 ? l1 : (k2 ? l2 : kPopLink);
+            sp = k1 ? i1 : i2;
+            if (link == kDoneLink) sp = 1;
+        }
+        const bool fresh = link < 0 && tri_i == tri_end;
+        int count = (link >> 28) & 7;
+        int first = link & 0x0FFFFFFF;
+        if (fresh && count == 0 && first < 0x0FFFFFFE) {     // a leaf with more than 7 triangles (rare)
+            const int2 bl = ldg(&b.big_leaves[first]);
+            first = bl.x;
+            count = bl.y;
+        }
+        tri_i = fresh ? first : tri_i;
+        tri_end = fresh ? first + count : tri_end;
+    }
+    template <class C>
+    RTB_HD void node_compute3(const float4 na, const float4 nb, const float4 nc, const int4 nd, C *cnt) {
+        float ml, mr;
+        const bool hl = box_test_z(r, na.x, na.y, na.z, na.w, nb.x, nb.y, ml);
+        const bool hr = box_test_z(r, nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, mr);
+        if (COUNT) cnt->box += 2;
+        const bool vl = hl && !(ml > cull), vr = hr && !(mr > cull);
+        const bool left_first = ((sgn >> nd.z) & 1u) != 0u;   // direction[split_dim] > 0 (bvh.cpp:183)
+        const bool both = vl && vr;
+        const bool take_left = both ? left_first : vl;
+        if (both) {
+            s_link[sp] = take_left ? nd.y : nd.x;
+            s_m[sp] = take_left ? mr : ml;
+            ++sp;
+        }
+        link = (vl || vr) ? (take_left ? nd.x : nd.y) : kPopLink;
+    }
+    template <class C>
+    RTB_HD void tri_compute3(const float4 q0, const float4 q1, const float4 q2, C *cnt) {
+        float t, u, v;
+        if (COUNT) cnt->tri += 1;
+        if (tri_test_flat(r, q0, q1, q2, t, u, v) && t < best.t) {
+            best.t = t;
+            best.u = u;
+            best.v = v;
+            best.id = tri_i;
+            cull = cull_bound(t, omax);
+        }
+        ++tri_i;
+        if (tri_i == tri_end) link = kPopLink;
+    }
+    template <class C>
+    RTB_HD void step3(const DBvh &b, C *cnt) {
+        pre3(b);
+        if (link >= 0) {
+            const DNode *np = b.nodes + link;
+            node_compute3(ldg(&np->a), ldg(&np->b), ldg(&np->c), ldg(&np->d), cnt);
+        } else if (tri_i < tri_end) {
+            const float4 *tp = b.tris + (size_t) tri_i * 3;
+            tri_compute3(ldg(tp), ldg(tp + 1), ldg(tp + 2), cnt);
+        }
+    }
     // whatever the lane's state asks for (host drivers; the device loops below schedule the steps per warp)
     template <class C>
     RTB_HD void step(const DBvh &b, C *cnt) {
@@ -228,6 +297,21 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
             } else {
                 if (doL) L.tri_step(b, cnt);
             }
+        } else if (MODE == 3) {
+            L.pre3(b);
+            const bool doN = L.link >= 0;
+            const bool doL = L.tri_i < L.tri_end;
+            const float4 *p = doN ? reinterpret_cast<const float4 *>(b.nodes + L.link) : (b.tris + (size_t) L.tri_i * 3);
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a, c = a;
+            int4 d = make_int4(0, 0, 0, 0);
+            if (doN || doL) {
+                a = __ldg(p);
+                bb = __ldg(p + 1);
+                c = __ldg(p + 2);
+            }
+            if (doN) d = __ldg(reinterpret_cast<const int4 *>(p + 3));
+            if (doN) L.node_compute3(a, bb, c, d, cnt);
+            if (doL) L.tri_compute3(a, bb, c, cnt);
         } else {
 #pragma unroll
             for (int step = 0; step < MODE; ++step) {

@@ -102,6 +102,42 @@ RTB_HD bool box_test_t(const Ray &r, float mnx, float mny, float mnz, float mxx,
     tmax = inside ? -1.f : tm;
     return inside || !bad;
 }
+// AABB::intersect once more, in the form the queue kernels run (fewest compare / select instructions; the first form
+// kept ~20 predicates alive per node and ptxas parked them in a bit mask, profiles/r02a_*).  Same decisions as
+// box_test_t for EVERY input, by these three observations:
+//  (1) Mid axes carry the sentinel -0.f instead of the reference's -1.  A sentinel only matters when no outside axis
+//      has a positive parameter (an outside axis' parameter is never +-0: |pl - o| >= the smallest subnormal and
+//      |inv| >= 1 - 2^-23 for a normalised direction).  Then the reference rejects unless the origin is inside
+//      (tmax < 0, primitive.cpp:193); here tm = -0, so every c_j = o_j + (-0 * d_j) = o_j exactly, which is in
+//      bounds exactly when axis j is Mid: all Mid (origin inside, primitive.cpp:172) -> accepted; an outside axis j
+//      is never whichPlane (a negative parameter loses against -0) -> rejected by its own bounds check.  The `inside`
+//      flag is therefore not computed at all.  tmax is -0 for an origin inside the box: never culled, like -1.
+//  (2) The `dir[i] != 0.` guards of primitive.cpp:178 are dropped: for a zero component of an outside axis the
+//      product is +-inf.  +inf becomes tm and sends every other coordinate with a non-zero direction to +-inf (out of
+//      bounds; there is one, the direction is normalised): rejected.  -inf never wins, and c_i = o_i + tm * 0 = o_i
+//      is outside: rejected.  The reference rejects both (t_i = -1, then either tmax < 0 or c_i = o_i fails).
+//  (3) An outside axis with a negative parameter moves away from its slab: c_i <= o_i < mn_i (or >= o_i > mx_i) by
+//      monotonic rounding, so it is rejected here as in the reference whichever plane is whichPlane.
+// tests/test_devsim.py::test_lane_form3_* pin this against the reference on random, axis-parallel and grid-aligned rays.
+RTB_HD bool box_test_z(const Ray &r, float mnx, float mny, float mnz, float mxx, float mxy, float mxz, float &tmax) {
+    const bool lo0 = r.o[0] < mnx, lo1 = r.o[1] < mny, lo2 = r.o[2] < mnz;
+    const bool out0 = lo0 || (r.o[0] > mxx), out1 = lo1 || (r.o[1] > mxy), out2 = lo2 || (r.o[2] > mxz);
+    const float t0 = out0 ? ((lo0 ? mnx : mxx) - r.o[0]) * r.inv[0] : -0.f;
+    const float t1 = out1 ? ((lo1 ? mny : mxy) - r.o[1]) * r.inv[1] : -0.f;
+    const float t2 = out2 ? ((lo2 ? mnz : mxz) - r.o[2]) * r.inv[2] : -0.f;
+    const bool w1 = t0 < t1;                 // whichPlane = 1 (unless 2 wins)
+    float tm = w1 ? t1 : t0;
+    const bool w2 = tm < t2;                 // whichPlane = 2
+    tm = w2 ? t2 : tm;
+    const float c0 = r.o[0] + tm * r.d[0];
+    const float c1 = r.o[1] + tm * r.d[1];
+    const float c2 = r.o[2] + tm * r.d[2];
+    const bool bad0 = (c0 < mnx) || (c0 > mxx);
+    const bool bad1 = (c1 < mny) || (c1 > mxy);
+    const bool bad2 = (c2 < mnz) || (c2 > mxz);
+    tmax = tm;
+    return !(((w1 || w2) && bad0) || ((!w1 || w2) && bad1) || (!w2 && bad2) || (tm < 0.f));
+}
 // see the header comment: tmax > cull_bound(best.t, omax) implies the reference's entry distance > best.t
 RTB_HD float ray_omax(const Ray &r) { return fmaxf(fmaxf(fabsf(r.o[0]), fabsf(r.o[1])), fabsf(r.o[2])); }
 RTB_HD float cull_bound(float best_t, float omax) { return best_t * 1.00001f + 1e-6f * omax; }

@@ -39,6 +39,42 @@ def box_rays(root_box, n, seed):
     return r
 
 
+def edge_rays(hs, root_box, n, seed):
+    """n rays built to sit ON the decision boundaries of the box test: axis-parallel and in-plane directions (zero
+    components), origins at triangle vertices (i.e. exactly on node-box planes), rays aimed exactly at vertices (the
+    corners of leaf boxes), origins one exact unit behind a box plane.  Pure function of (scene, n, seed)."""
+    u = gen_scenes.splitmix_u01(seed, 0, n * 8).reshape(n, 8)
+    pos = hs.tris()["pos"]
+    p0 = pos[:, 0:3]
+    verts = np.concatenate([p0, p0 + pos[:, 3:6], p0 + pos[:, 6:9]]).astype(np.float32)
+    lo = np.asarray(root_box[:3], np.float32)
+    hi = np.asarray(root_box[3:], np.float32)
+    rnd = ((lo + hi) * np.float32(0.5) + (u[:, 0:3] * np.float32(2) - np.float32(1)) * (hi - lo) * np.float32(0.625)).astype(np.float32)
+    va = verts[np.minimum((u[:, 3] * len(verts)).astype(np.int64), len(verts) - 1)]
+    vb = verts[np.minimum((u[:, 4] * len(verts)).astype(np.int64), len(verts) - 1)]
+    axis = np.minimum((u[:, 5] * 3).astype(np.int64), 2)
+    sign = np.where(u[:, 6] < 0.5, np.float32(-1), np.float32(1)).astype(np.float32)
+    e = np.zeros((n, 3), np.float32)
+    e[np.arange(n), axis] = sign
+    kind = np.minimum((u[:, 7] * 6).astype(np.int64), 5)
+    r = np.empty((n, 6), np.float32)
+    rd = (u[:, 0:3] * np.float32(2) - np.float32(1)).astype(np.float32)
+    planar = rd.copy()
+    planar[np.arange(n), axis] = 0
+    for k, (o, d) in enumerate([(va, e),                      # from a vertex along an axis
+                                (rnd, e),                     # anywhere, along an axis
+                                (rnd, planar),                # one zero component
+                                (rnd, va - rnd),              # aimed exactly at a vertex
+                                (va - e, e),                  # exactly one unit behind a vertex, along the axis through it
+                                (va, vb - va)]):              # vertex to vertex
+        m = kind == k
+        r[m, 0:3] = o[m]
+        r[m, 3:6] = d[m]
+    bad = np.all(r[:, 3:6] == 0, axis=1)
+    r[bad, 3:6] = np.float32(1)
+    return r
+
+
 def camera_rays(cam, n, seed):
     """n rays from the camera position into the view cone (what primary rays look like), un-normalised."""
     u = gen_scenes.splitmix_u01(seed, 0, n * 2).reshape(n, 2)

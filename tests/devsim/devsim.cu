@@ -98,8 +98,9 @@ int devsim_closest_hit_lane(const rtb_scene_desc *desc, const float *rays6, size
         make_ray(L.r, rays6[i * 6], rays6[i * 6 + 1], rays6[i * 6 + 2], rays6[i * 6 + 3], rays6[i * 6 + 4], rays6[i * 6 + 5]);
         Counters c = {0, 0};
         L.begin(s.d.bvh, &c);
-        (void) schedule_seed;
-        while (!L.finished()) L.step(s.d.bvh, &c);
+        // schedule_seed selects the form of the state machine: 3 = one pop / decode site per step (MODE 3), else the first form
+        if (schedule_seed == 3u) while (!L.finished()) L.step3(s.d.bvh, &c);
+        else while (!L.finished()) L.step(s.d.bvh, &c);
         box += c.box;
         tri += c.tri;
         const bool ok = L.best.id >= 0;

@@ -41,6 +41,54 @@ def test_queue_lane_state_machine(name, host_scene):
     assert np.array_equal(cam["id"], g["cam_hit_id"]) and np.array_equal(cam["t"], g["cam_hit_t"])
 
 
+@pytest.mark.parametrize("name", SCENES)
+def test_lane_form3_equals_first_form(name, host_scene):
+    """form 3 of the lane state machine (one pop / decode site per step, box test without the `inside` flag and the
+    zero-direction guards: rtb_traverse.cuh box_test_z) = the reference's hits, with exactly the first form's tests"""
+    g = _util.load_golden(name)
+    hs = host_scene(name)
+    rays = _util.box_rays(g["root_box"], g["hit_id"].shape[0], seed=1000)
+    h = _util.devsim_closest_hit_lane(hs, rays, 3)
+    assert np.array_equal(h["id"], g["hit_id"])
+    for k in ("t", "u", "v"):
+        assert np.array_equal(h[k], g["hit_" + k]), k
+    first = _util.devsim_closest_hit_lane(hs, rays, 0)
+    assert (h["box_tests"], h["tri_tests"]) == (first["box_tests"], first["tri_tests"])
+    cam = _util.devsim_closest_hit_lane(hs, _util.camera_rays(_util.golden_camera(g), g["cam_hit_id"].shape[0], seed=2000), 3)
+    assert np.array_equal(cam["id"], g["cam_hit_id"]) and np.array_equal(cam["t"], g["cam_hit_t"])
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_lane_form3_on_decision_boundaries(name, host_scene):
+    """rays that sit on the box test's decision boundaries (zero direction components, origins on box planes, rays
+    through box corners): form 3 vs the twin (the pinned restatement of the reference's recursion)"""
+    g = _util.load_golden(name)
+    hs = host_scene(name)
+    rays = _util.edge_rays(hs, g["root_box"], 60000, seed=77)
+    first = _util.devsim_closest_hit_lane(hs, rays, 0)
+    h = _util.devsim_closest_hit_lane(hs, rays, 3)
+    # the same visits (box_test_z decides like box_test_t on every box met) and the same answers, bit for bit
+    assert (h["box_tests"], h["tri_tests"]) == (first["box_tests"], first["tri_tests"])
+    for k in ("id", "t", "u", "v"):
+        assert np.array_equal(h[k], first[k]), k
+    # against the reference's recursion.  Rays aimed exactly at a shared vertex are the documented tie case of global-best
+    # culling (DESIGN.md section 3): several triangles answer with parameters a few ulp apart and the reference's
+    # sibling-only culling keeps whichever its rounded entry distance lets through; global-best culling returns the
+    # smallest.  Everything else must agree exactly.
+    want = _util.twin_bvh(hs).closest_hit(rays)
+    assert np.array_equal(h["id"] >= 0, want["id"] >= 0)
+    hit = want["id"] >= 0
+    same = h["id"] == want["id"]
+    for k in ("t", "u", "v"):
+        assert np.array_equal(h[k][hit & same], want[k][hit & same]), k
+    tie = hit & ~same
+    assert np.count_nonzero(tie) <= 0.005 * rays.shape[0]
+    assert np.all(h["t"][tie] <= want["t"][tie])
+    # (a grazing triangle's parameter is ill-conditioned: the two candidates were seen up to 7e-5 apart)
+    assert np.all(np.abs(h["t"][tie] - want["t"][tie]) <= 1e-3 * want["t"][tie])
+    assert 0.05 < np.mean(hit) < 0.999
+
+
 @pytest.mark.parametrize("name", ["s6_1", "soup_10k"])
 def test_reference_cull_counts_equal_twin(name, host_scene):
     """CULL_REFERENCE visits exactly the boxes and triangles the reference's recursion visits"""
