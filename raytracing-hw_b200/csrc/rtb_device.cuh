@@ -61,6 +61,7 @@ struct __align__(16) DNode {
 
 constexpr int kLeafFlag = (int) 0x80000000u;
 constexpr int kMaxStack = 64;
+constexpr int kTriStride = 4;   // float4 per triangle record (the 4th is padding: a 48-byte record already costs two 32-byte sectors)
 constexpr float kFar = 1e9f;   // `intersection.distance = 1e9` (bvh.cpp:181)
 
 struct DTexture {
@@ -70,7 +71,8 @@ struct DTexture {
 
 struct DBvh {
     const DNode *nodes;       // internal nodes only
-    const float4 *tris;       // 3 x float4 per triangle: (p0.xyz, U.x) (U.yz, V.xy) (V.z, Ng.xyz)
+    const float4 *tris;       // kTriStride x float4 per triangle: (p0.xyz, U.x) (U.yz, V.xy) (V.z, Ng.xyz) (pad): 64-byte records,
+                              // so that node and triangle records are both fetched with two 256-bit loads (rtb_trace.cuh)
     const int2 *big_leaves;   // {first, count}
     float root_box[6];
     int root_link;            // link of the root (a leaf link when the whole BVH is one leaf)
@@ -299,7 +301,7 @@ RTB_HD bool closest_hit_ordered(const DBvh &b, const Ray &r, Hit &best, Counters
             int first, count;
             decode_leaf(b, link, first, count);
             for (int i = first; i < first + count; ++i) {
-                const float4 *tp = b.tris + (size_t) i * 3;
+                const float4 *tp = b.tris + (size_t) i * kTriStride;
                 const float4 q0 = ldg(tp), q1 = ldg(tp + 1), q2 = ldg(tp + 2);
                 float t, u, v;
                 if (COUNT) cnt->tri += 1;
@@ -368,7 +370,7 @@ RTB_HD void all_hits(const DBvh &b, const Ray &r, Counters *cnt, F f) {
             int first, count;
             decode_leaf(b, link, first, count);
             for (int i = first; i < first + count; ++i) {
-                const float4 *tp = b.tris + (size_t) i * 3;
+                const float4 *tp = b.tris + (size_t) i * kTriStride;
                 const float4 q0 = ldg(tp), q1 = ldg(tp + 1), q2 = ldg(tp + 2);
                 float t, u, v;
                 if (COUNT) cnt->tri += 1;

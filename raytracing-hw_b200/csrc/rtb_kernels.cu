@@ -33,7 +33,7 @@ __global__ void __launch_bounds__(128) k_closest_hit(const __grid_constant__ DSc
             uint8_t in = 0;
             if (ok) {
                 // `if (dot(ray.direction, normal) > 0) inside = true` (primitive.cpp:51-54)
-                const float4 q2 = __ldg(sc.bvh.tris + (size_t) h.id * 3 + 2);
+                const float4 q2 = __ldg(sc.bvh.tris + (size_t) h.id * kTriStride + 2);
                 float dn = r.d[0] * q2.y;
                 dn = dn + r.d[1] * q2.z;
                 dn = dn + r.d[2] * q2.w;
@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(128, MINB) k_closest_hit_queue(const __grid_co
                                                            float *__restrict__ t, float *__restrict__ u, float *__restrict__ v,
                                                            uint8_t *__restrict__ inside, unsigned long long *__restrict__ counters,
                                                            const TracePolicy pol) {
-    QueueCounters cnt = {0ull, 0ull, 0ull};
+    QueueCounters cnt = {0ull, 0ull, 0u};
     trace_persistent<COUNT, MODE>(
         sc.bvh, n, queue_head,
         [&](unsigned i, Ray &r, unsigned &tag) {
@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(128, MINB) k_closest_hit_queue(const __grid_co
             if (inside) {
                 uint8_t in = 0;
                 if (ok) {   // `if (dot(ray.direction, normal) > 0) inside = true` (primitive.cpp:51-54)
-                    const float4 q2 = __ldg(sc.bvh.tris + (size_t) h.id * 3 + 2);
+                    const float4 q2 = __ldg(sc.bvh.tris + (size_t) h.id * kTriStride + 2);
                     float dn = r.d[0] * q2.y;
                     dn = dn + r.d[1] * q2.z;
                     dn = dn + r.d[2] * q2.w;

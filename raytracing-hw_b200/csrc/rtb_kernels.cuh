@@ -10,7 +10,7 @@ void launch_closest_hit(const DScene &sc, const float *d_rays6, size_t n, int cu
 int persistent_grid(int threads_per_block, int blocks_per_sm);
 constexpr int kDefaultTraceMode = 3;       // rtb_trace.cuh: 0 = voted phases, 1 = unified step, 3 = unified step with one pop / decode site (RTB_TRACE_MODE)
 int trace_mode();
-constexpr int kDefaultTraceBlocks = 9;    // sweeps: profiles/r01d_closest_hit_blocks_sweep.jsonl (first form), profiles/r02a_mode3_sweep.txt (form 3)
+constexpr int kDefaultTraceBlocks = 9;    // sweeps: profiles/r01d_closest_hit_blocks_sweep.jsonl (first form), profiles/r01i_mode3_sweep.txt (form 3)
 int persistent_blocks_per_sm();   // CTAs per SM of the persistent queue kernels (RTB_TRACE_BLOCKS overrides)
 
 void launch_light_pdf(const DScene &sc, const float *d_rays6, size_t n, float *d_pdf, cudaStream_t stream);

@@ -37,7 +37,7 @@ inline bool convert_bvh(uint32_t n_nodes, const float *aabb, const int32_t *link
     if (n_nodes == 0 || n_tris == 0) { err = "empty BVH"; return false; }
     if (n_tris >= (1u << 28)) { err = "too many triangles for the 28-bit leaf link"; return false; }
     // triangles: (p0.xyz, U.x) (U.yz, V.xy) (V.z, Ng.xyz); Ng = get_geometric_normal (primitive.cpp:77-84)
-    o.tris.resize((size_t) n_tris * 3);
+    o.tris.assign((size_t) n_tris * kTriStride, make_float4(0.f, 0.f, 0.f, 0.f));
     o.inv_area.resize(n_tris);
     for (uint32_t i = 0; i < n_tris; ++i) {
         const float *p = tri_pos + (size_t) i * 9;
@@ -49,9 +49,9 @@ inline bool convert_bvh(uint32_t n_nodes, const float *aabb, const int32_t *link
         const float area = 0.5f * len;
         const float mod = 1.f / len;
         for (int k = 0; k < 3; ++k) n[k] *= mod;
-        o.tris[(size_t) i * 3 + 0] = make_float4(p[0], p[1], p[2], U[0]);
-        o.tris[(size_t) i * 3 + 1] = make_float4(U[1], U[2], V[0], V[1]);
-        o.tris[(size_t) i * 3 + 2] = make_float4(V[2], n[0], n[1], n[2]);
+        o.tris[(size_t) i * kTriStride + 0] = make_float4(p[0], p[1], p[2], U[0]);
+        o.tris[(size_t) i * kTriStride + 1] = make_float4(U[1], U[2], V[0], V[1]);
+        o.tris[(size_t) i * kTriStride + 2] = make_float4(V[2], n[0], n[1], n[2]);
         o.inv_area[i] = 1.f / area;   // `probability = 1.f / triangle_area` (random.cpp:88)
     }
     std::memcpy(o.root_box, aabb, 24);

@@ -207,7 +207,7 @@ RTB_HD V3 sample_light(const DScene &sc, V3 point, Rng &g) {
         u = 1.f - u;
         v = 1.f - v;
     }
-    const float4 *tp = sc.light_bvh.tris + (size_t) pick * 3;
+    const float4 *tp = sc.light_bvh.tris + (size_t) pick * kTriStride;
     const float4 q0 = ldg(tp), q1 = ldg(tp + 1), q2 = ldg(tp + 2);
     const V3 o = V3{q0.x, q0.y, q0.z}, U = V3{q0.w, q1.x, q1.y}, Vv = V3{q1.z, q1.w, q2.x};
     const V3 res = (o + u * U) + v * Vv;
@@ -429,7 +429,7 @@ RTB_HD V3 trace_path(const DScene &sc, Ray r, Rng &g, PathCounters *pc) {
         pc->rays += 1;
         const bool ok = closest_hit<CULL, COUNT>(sc.bvh, r, h, COUNT ? &pc->tests : nullptr);
         if (!(ok && h.t < sc.max_distance)) break;   // miss: `intersection.object_id >= objects.size()` -> unsuccessful
-        const float4 q2 = ldg(sc.bvh.tris + (size_t) h.id * 3 + 2);
+        const float4 q2 = ldg(sc.bvh.tris + (size_t) h.id * kTriStride + 2);
         V3 Ng = V3{q2.y, q2.z, q2.w};
         const V3 rd = V3{r.d[0], r.d[1], r.d[2]};
         const bool inside = dot(rd, Ng) > 0.f;   // primitive.cpp:51-54

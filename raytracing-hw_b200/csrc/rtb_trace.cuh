@@ -20,7 +20,8 @@ struct TracePolicy;
 TracePolicy trace_policy();   // rtb_kernels.cu
 
 struct QueueCounters {
-    unsigned long long box, tri, rays;
+    unsigned long long box, tri;
+    unsigned rays;          // per lane and launch
 };
 
 // Phase vote of a warp iteration: refill when at least `refill_min` lanes are idle (or nothing else is runnable);
@@ -47,6 +48,7 @@ struct LaneTraversal {
     // out of this struct lets every other member be promoted to registers
     int *s_link;
     float *s_m;
+    int2 *s2;               // form 3: one array of {link, entry parameter} pairs (one 64-bit local access per entry)
     int sp;
     int link;
     int tri_i, tri_end;
@@ -68,6 +70,22 @@ struct LaneTraversal {
         sgn = 0u;
         best.t = kFar; best.u = 0.f; best.v = 0.f; best.id = -1;
         for (int k = 0; k < 3; ++k) { r.o[k] = 0.f; r.d[k] = 0.f; r.inv[k] = 0.f; }
+    }
+    RTB_HD void reset3(int2 *stack) {
+        reset(reinterpret_cast<int *>(stack), reinterpret_cast<float *>(stack) + 1);   // (the first form's arrays are not used)
+        s2 = stack;
+        s2[0] = make_int2(kDoneLink, (int) f2u(-1.f));   // the sentinel is never culled
+        s2[kUvSlot] = make_int2(0, 0);
+    }
+    // form 3 keeps what only the end of a ray needs out of the registers (the 48 / 56-register budgets of 10 / 9 CTAs
+    // per SM): the barycentrics of the best hit live in a fixed local-memory slot above the stack (one predicated 64-bit
+    // store per improvement, one load per ray) and max|origin| is recomputed when a hit improves.
+    static constexpr int kUvSlot = kMaxStack + 1;
+    static constexpr int kStack3 = kMaxStack + 2;          // entries of the form-3 array
+    RTB_HD void finish3() {
+        const int2 uv = s2[kUvSlot];
+        best.u = u2f((uint32_t) uv.x);
+        best.v = u2f((uint32_t) uv.y);
     }
     RTB_HD bool wants_node() const { return link >= 0; }
     RTB_HD bool wants_tri() const { return tri_i < tri_end; }
@@ -155,7 +173,7 @@ struct LaneTraversal {
     }
     template <class C>
     RTB_HD void tri_step(const DBvh &b, C *cnt) {
-        const float4 *tp = b.tris + (size_t) tri_i * 3;
+        const float4 *tp = b.tris + (size_t) tri_i * kTriStride;
         const float4 q0 = ldg(tp), q1 = ldg(tp + 1), q2 = ldg(tp + 2);
         tri_compute(b, q0, q1, q2, cnt);
     }
@@ -168,10 +186,9 @@ struct LaneTraversal {
     RTB_HD void pre3(const DBvh &b) {
         if (link == kPopLink) {
             const int i1 = sp - 1, i2 = sp >= 2 ? sp - 2 : 0;
-            const int l1 = s_link[i1], l2 = s_link[i2];
-            const float m1 = s_m[i1], m2 = s_m[i2];
-            const bool k1 = !(m1 > cull), k2 = !(m2 > cull);
-            link = k1 ? l1 : (k2 ? l2 : kPopLink);
+            const int2 e1 = s2[i1], e2 = s2[i2];
+            const bool k1 = !(u2f((uint32_t) e1.y) > cull), k2 = !(u2f((uint32_t) e2.y) > cull);
+            link = k1 ? e1.x : (k2 ? e2.x : kPopLink);
             sp = k1 ? i1 : i2;
             if (link == kDoneLink) sp = 1;
         }
@@ -195,10 +212,9 @@ struct LaneTraversal {
         const bool vl = hl && !(ml > cull), vr = hr && !(mr > cull);
         const bool left_first = ((sgn >> nd.z) & 1u) != 0u;   // direction[split_dim] > 0 (bvh.cpp:183)
         const bool both = vl && vr;
-        const bool take_left = both ? left_first : vl;
+        const bool take_left = vl && (left_first || !vr);    // both ? left_first : vl
         if (both) {
-            s_link[sp] = take_left ? nd.y : nd.x;
-            s_m[sp] = take_left ? mr : ml;
+            s2[sp] = make_int2(take_left ? nd.y : nd.x, (int) f2u(take_left ? mr : ml));
             ++sp;
         }
         link = (vl || vr) ? (take_left ? nd.x : nd.y) : kPopLink;
@@ -209,10 +225,9 @@ struct LaneTraversal {
         if (COUNT) cnt->tri += 1;
         if (tri_test_flat(r, q0, q1, q2, t, u, v) && t < best.t) {
             best.t = t;
-            best.u = u;
-            best.v = v;
             best.id = tri_i;
-            cull = cull_bound(t, omax);
+            s2[kUvSlot] = make_int2((int) f2u(u), (int) f2u(v));
+            cull = cull_bound(t, ray_omax(r));
         }
         ++tri_i;
         if (tri_i == tri_end) link = kPopLink;
@@ -224,7 +239,7 @@ struct LaneTraversal {
             const DNode *np = b.nodes + link;
             node_compute3(ldg(&np->a), ldg(&np->b), ldg(&np->c), ldg(&np->d), cnt);
         } else if (tri_i < tri_end) {
-            const float4 *tp = b.tris + (size_t) tri_i * 3;
+            const float4 *tp = b.tris + (size_t) tri_i * kTriStride;
             tri_compute3(ldg(tp), ldg(tp + 1), ldg(tp + 2), cnt);
         }
     }
@@ -238,6 +253,17 @@ struct LaneTraversal {
 };
 
 #ifdef __CUDACC__
+// 32 bytes through the read-only path in one instruction (p 32-byte aligned)
+__device__ __forceinline__ void ldg256(const float4 *p, float4 &lo, float4 &hi) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w)
+                 : "l"(p));
+}
+__device__ __forceinline__ void ldg256(const float4 *p, float4 &lo, int4 &hi) {
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=r"(hi.x), "=r"(hi.y), "=r"(hi.z), "=r"(hi.w)
+                 : "l"(p));
+}
 // Fetch(idx, Ray&, tag&) loads queue entry `idx` (normalising as Ray::Ray does) and returns false when the entry holds
 // no ray (a finished slot of the wavefront integrator); Emit(tag, ray, hit) stores the result of the entry's ray.
 //
@@ -253,10 +279,10 @@ template <bool COUNT, int MODE, class Fetch, class Emit>
 __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsigned *queue_head, Fetch fetch, Emit emit, QueueCounters *cnt, const TracePolicy pol) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    int stack_link[kMaxStack + 1];
-    float stack_m[kMaxStack + 1];
+    __align__(8) int2 stack[LaneTraversal<COUNT>::kStack3];
     LaneTraversal<COUNT> L;
-    L.reset(stack_link, stack_m);
+    if (MODE == 3) L.reset3(stack);
+    else L.reset(reinterpret_cast<int *>(stack), reinterpret_cast<float *>(stack) + kMaxStack + 1);
     unsigned tag = 0;
     bool have_ray = false, exhausted = false;
 
@@ -273,7 +299,10 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
             if (lane == leader) base = atomicAdd(queue_head, (unsigned) cR);
             base = __shfl_sync(FULL, base, leader);
             if (wantR) {
-                if (have_ray) emit(tag, L.r, L.best);
+                if (have_ray) {
+                    if (MODE == 3) L.finish3();
+                    emit(tag, L.r, L.best);
+                }
                 const unsigned idx = base + (unsigned) __popc(mR & ((1u << lane) - 1u));
                 if (idx < n) {
                     have_ray = fetch(idx, L.r, tag);
@@ -301,15 +330,15 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
             L.pre3(b);
             const bool doN = L.link >= 0;
             const bool doL = L.tri_i < L.tri_end;
-            const float4 *p = doN ? reinterpret_cast<const float4 *>(b.nodes + L.link) : (b.tris + (size_t) L.tri_i * 3);
-            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a, c = a;
-            int4 d = make_int4(0, 0, 0, 0);
-            if (doN || doL) {
-                a = __ldg(p);
-                bb = __ldg(p + 1);
-                c = __ldg(p + 2);
-            }
-            if (doN) d = __ldg(reinterpret_cast<const int4 *>(p + 3));
+            // One 64-byte record per lane -- its node or its triangle -- with two 256-bit loads (LDG.E.256, new on
+            // sm_100): half the load instructions and half the LSU wavefronts of the 4 x LDG.128 form, which ncu showed
+            // at 81 % of the LSU data-pipe peak (profiles/r01i_k_wf_trace_summary.txt).  Idle lanes (waiting for a
+            // refill or for their next pop) read triangle 0: no predicates, no zeroing.
+            const float4 *p = doN ? reinterpret_cast<const float4 *>(b.nodes + L.link) : (b.tris + (size_t) (doL ? L.tri_i : 0) * kTriStride);
+            float4 a, bb, c;
+            int4 d;
+            ldg256(p, a, bb);
+            ldg256(p + 2, c, d);
             if (doN) L.node_compute3(a, bb, c, d, cnt);
             if (doL) L.tri_compute3(a, bb, c, cnt);
         } else {
@@ -319,7 +348,7 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
                 const bool doN = L.wants_node();
                 const bool doL = L.wants_tri();
                 // one fetch stage for both kinds of record
-                const float4 *p = doN ? reinterpret_cast<const float4 *>(b.nodes + L.link) : (b.tris + (size_t) L.tri_i * 3);
+                const float4 *p = doN ? reinterpret_cast<const float4 *>(b.nodes + L.link) : (b.tris + (size_t) L.tri_i * kTriStride);
                 float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a, c = a;
                 int4 d = make_int4(0, 0, 0, 0);
                 if (doN || doL) {

@@ -103,7 +103,7 @@ RTB_HD bool box_test_t(const Ray &r, float mnx, float mny, float mnz, float mxx,
     return inside || !bad;
 }
 // AABB::intersect once more, in the form the queue kernels run (fewest compare / select instructions; the first form
-// kept ~20 predicates alive per node and ptxas parked them in a bit mask, profiles/r02a_*).  Same decisions as
+// kept ~20 predicates alive per node and ptxas parked them in a bit mask, profiles/r01h_k_wf_trace_lines.txt).  Same decisions as
 // box_test_t for EVERY input, by these three observations:
 //  (1) Mid axes carry the sentinel -0.f instead of the reference's -1.  A sentinel only matters when no outside axis
 //      has a positive parameter (an outside axis' parameter is never +-0: |pl - o| >= the smallest subnormal and
@@ -234,7 +234,7 @@ RTB_HD bool closest_hit_global(const DBvh &b, const Ray &r, Hit &best, Counters 
             int first, count;
             decode_leaf(b, link, first, count);
             for (int i = first; i < first + count; ++i) {
-                const float4 *tp = b.tris + (size_t) i * 3;
+                const float4 *tp = b.tris + (size_t) i * kTriStride;
                 const float4 q0 = ldg(tp), q1 = ldg(tp + 1), q2 = ldg(tp + 2);
                 float t, u, v;
                 if (COUNT) cnt->tri += 1;

@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(const __grid_constant__ 
     // the grid was sized on the host for the list's capacity; when few slots are still active, the surplus CTAs leave
     // at once so that every remaining lane still pulls several rays from the queue (dynamic balance needs that)
     if (n == 0 || (blockIdx.x > 0 && blockIdx.x * (128u * rays_per_lane) >= n)) return;
-    QueueCounters cnt = {0ull, 0ull, 0ull};
+    QueueCounters cnt = {0ull, 0ull, 0u};
     trace_persistent<COUNT, MODE>(
         sc.bvh, n, queue_head,
         [&](unsigned i, Ray &r, unsigned &tag) {
@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(const __grid_constant__ 
             }
         }
         if ((threadIdx.x & 31) == 0) {
-            if (cnt.rays) atomicAdd(&counters[0], cnt.rays);
+            if (cnt.rays) atomicAdd(&counters[0], (unsigned long long) cnt.rays);
             if (COUNT) {
                 atomicAdd(&counters[2], cnt.box);
                 atomicAdd(&counters[3], cnt.tri);

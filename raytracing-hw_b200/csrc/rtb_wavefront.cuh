@@ -98,7 +98,7 @@ RTB_HD unsigned wf_shade_slot(const DScene &sc, const RenderLaunch &p, const WfS
     V3 last = V3{0.f, 0.f, 0.f};      // colour of the deepest successful vertex when the path ends at a hit
     bool last_is_hit = false;
     if (h.id >= 0 && h.t < sc.max_distance) {
-        const float4 q2 = ldg(sc.bvh.tris + (size_t) h.id * 3 + 2);
+        const float4 q2 = ldg(sc.bvh.tris + (size_t) h.id * kTriStride + 2);
         V3 Ng = V3{q2.y, q2.z, q2.w};
         const V3 rd = V3{r.d[0], r.d[1], r.d[2]};
         const bool inside = dot(rd, Ng) > 0.f;   // primitive.cpp:51-54

@@ -73,7 +73,7 @@ int devsim_closest_hit(const rtb_scene_desc *desc, const float *rays6, size_t n,
         if (inside) {
             uint8_t in = 0;
             if (ok) {
-                const float4 q2 = s.d.bvh.tris[(size_t) h.id * 3 + 2];
+                const float4 q2 = s.d.bvh.tris[(size_t) h.id * kTriStride + 2];
                 in = dot(V3{r.d[0], r.d[1], r.d[2]}, V3{q2.y, q2.z, q2.w}) > 0.f ? 1 : 0;
             }
             inside[i] = in;
@@ -93,13 +93,15 @@ int devsim_closest_hit_lane(const rtb_scene_desc *desc, const float *rays6, size
     for (size_t i = 0; i < n; ++i) {
         int stack_link[kMaxStack + 1];
         float stack_m[kMaxStack + 1];
+        int2 stack2[LaneTraversal<true>::kStack3];
         LaneTraversal<true> L;
         L.reset(stack_link, stack_m);
+        if (schedule_seed == 3u) L.reset3(stack2);
         make_ray(L.r, rays6[i * 6], rays6[i * 6 + 1], rays6[i * 6 + 2], rays6[i * 6 + 3], rays6[i * 6 + 4], rays6[i * 6 + 5]);
         Counters c = {0, 0};
         L.begin(s.d.bvh, &c);
         // schedule_seed selects the form of the state machine: 3 = one pop / decode site per step (MODE 3), else the first form
-        if (schedule_seed == 3u) while (!L.finished()) L.step3(s.d.bvh, &c);
+        if (schedule_seed == 3u) { while (!L.finished()) L.step3(s.d.bvh, &c); L.finish3(); }
         else while (!L.finished()) L.step(s.d.bvh, &c);
         box += c.box;
         tri += c.tri;
