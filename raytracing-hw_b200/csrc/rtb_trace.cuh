@@ -281,7 +281,7 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
     const int lane = threadIdx.x & 31;
     __align__(8) int2 stack[LaneTraversal<COUNT>::kStack3];
     LaneTraversal<COUNT> L;
-    if (MODE == 3) L.reset3(stack);
+    if (MODE >= 3) L.reset3(stack);
     else L.reset(reinterpret_cast<int *>(stack), reinterpret_cast<float *>(stack) + kMaxStack + 1);
     unsigned tag = 0;
     bool have_ray = false, exhausted = false;
@@ -300,7 +300,7 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
             base = __shfl_sync(FULL, base, leader);
             if (wantR) {
                 if (have_ray) {
-                    if (MODE == 3) L.finish3();
+                    if (MODE >= 3) L.finish3();
                     emit(tag, L.r, L.best);
                 }
                 const unsigned idx = base + (unsigned) __popc(mR & ((1u << lane) - 1u));
@@ -326,7 +326,12 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
             } else {
                 if (doL) L.tri_step(b, cnt);
             }
-        } else if (MODE == 3) {
+        } else if (MODE >= 3) {
+            // MODE 3 / 4 / 5: one / two / three steps per refill vote (profiles/r01j_sched_sweep.txt: two is best, +2 %).
+            // Gating the triangle code on the number of lanes holding a triangle (they wait a step unless >= 4 / 8 / 12
+            // want it) was measured there too and loses 4 / 6 / 10 %: a ray's latency matters more than the issue slots.
+#pragma unroll
+            for (int step = 0; step < MODE - 2; ++step) {
             L.pre3(b);
             const bool doN = L.link >= 0;
             const bool doL = L.tri_i < L.tri_end;
@@ -341,6 +346,7 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
             ldg256(p + 2, c, d);
             if (doN) L.node_compute3(a, bb, c, d, cnt);
             if (doL) L.tri_compute3(a, bb, c, cnt);
+            }
         } else {
 #pragma unroll
             for (int step = 0; step < MODE; ++step) {

@@ -341,7 +341,7 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
             else if (bps <= 9) RTB_LAUNCH_T(false, 9, MODE);         \
             else if (bps <= 10) RTB_LAUNCH_T(false, 10, MODE);       \
             else RTB_LAUNCH_T(false, 12, MODE)
-            if (mode == 0) { RTB_LAUNCH_TM(0); } else if (mode == 1) { RTB_LAUNCH_TM(1); } else { RTB_LAUNCH_TM(3); }
+            if (mode == 0) { RTB_LAUNCH_TM(0); } else if (mode == 1) { RTB_LAUNCH_TM(1); } else if (mode == 4) { RTB_LAUNCH_TM(4); } else if (mode == 5) { RTB_LAUNCH_TM(5); } else { RTB_LAUNCH_TM(3); }
 #undef RTB_LAUNCH_TM
 #undef RTB_LAUNCH_T
             mark();
