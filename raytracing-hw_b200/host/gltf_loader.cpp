@@ -6,12 +6,15 @@
 //
 // Known reference quirks kept on purpose: parents must precede children in `nodes`;
 // camera axes are divided by the node scale; zfar>0 becomes the hit-distance limit of every ray; a non-zero file
-// aspectRatio overrides W/H; alphaMode / doubleSided / KHR_materials_specular are ignored; no byteStride.
+// aspectRatio overrides W/H; alphaMode / doubleSided / KHR_materials_specular are ignored.
+// Beyond the reference: bufferView.byteStride (interleaved vertex buffers) and the binary
+// .glb container are accepted; tightly packed .gltf files load exactly as before.
 // One deliberate deviation: a primitive WITHOUT a NORMAL attribute reads uninitialised `indices_count` in the
 // reference (scene_parser.cpp:204-234, UB); here it gets the accessor's count and normal (0,0,1).
 #include "host_scene.h"
 #include "json.h"
 
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <fstream>
@@ -165,15 +168,42 @@ struct View {
     size_t count = 0;
     int component_type = 0;
     std::string type;
+    size_t stride = 0;      // bytes between elements: bufferView.byteStride, or the element size when tightly packed
+    const uint8_t *at(size_t i) const { return ptr + i * stride; }
 };
 
 }  // namespace
 
 void load_gltf(const std::string &filename, int width, int height, int samples, HostScene &scene) {
     std::string text;
+    std::vector<uint8_t> glb_bin;     // the BIN chunk of a binary glTF container (buffer 0 when it has no uri)
+    bool is_glb = false;
     {
         std::vector<uint8_t> raw = read_file(filename);
-        text.assign(raw.begin(), raw.end());
+        auto u32 = [&](size_t off) { uint32_t x; std::memcpy(&x, raw.data() + off, 4); return x; };
+        if (raw.size() >= 20 && std::memcmp(raw.data(), "glTF", 4) == 0) {
+            // .glb (beyond the reference, which only calls LoadASCIIFromFile: scene_parser.cpp:33): 12-byte header,
+            // then chunks {length, type, data}: JSON first, an optional BIN after it
+            is_glb = true;
+            const size_t total = std::min<size_t>(u32(8), raw.size());
+            size_t off = 12;
+            bool have_json = false;
+            while (off + 8 <= total) {
+                const size_t len = u32(off);
+                const uint32_t type = u32(off + 4);
+                if (off + 8 + len > total) throw std::runtime_error("[tinygltf] Failed to parse \"" + filename + "\"");
+                if (type == 0x4E4F534Au && !have_json) {          // "JSON"
+                    text.assign(raw.begin() + (ptrdiff_t) (off + 8), raw.begin() + (ptrdiff_t) (off + 8 + len));
+                    have_json = true;
+                } else if (type == 0x004E4942u && glb_bin.empty()) {   // "BIN\0"
+                    glb_bin.assign(raw.begin() + (ptrdiff_t) (off + 8), raw.begin() + (ptrdiff_t) (off + 8 + len));
+                }
+                off += 8 + ((len + 3) & ~(size_t) 3);
+            }
+            if (!have_json) throw std::runtime_error("[tinygltf] Failed to parse \"" + filename + "\"");
+        } else {
+            text.assign(raw.begin(), raw.end());
+        }
     }
     Json model;
     try {
@@ -278,6 +308,10 @@ void load_gltf(const std::string &filename, int width, int height, int samples, 
     std::vector<std::vector<uint8_t>> buffers(jbuffers.size());
     for (size_t i = 0; i < jbuffers.size(); ++i) {
         const std::string uri = jbuffers.at(i).string_or("uri", "");
+        if (uri.empty() && is_glb && i == 0) {
+            buffers[i] = std::move(glb_bin);
+            continue;
+        }
         if (uri.empty()) throw std::runtime_error("[tinygltf] Failed to parse \"" + filename + "\"");
         try {
             buffers[i] = load_uri(uri, base_dir);
@@ -289,10 +323,13 @@ void load_gltf(const std::string &filename, int width, int height, int samples, 
 
     // ---- textures = images, always RGBA8 (scene_parser.cpp:131-142)
     const Json &jimages = arr("images");
+    std::vector<std::vector<uint8_t>> image_bytes(jimages.size());
+    std::vector<std::string> image_uri(jimages.size());
     for (size_t i = 0; i < jimages.size(); ++i) {
         const Json &ji = jimages.at(i);
-        std::vector<uint8_t> bytes;
+        std::vector<uint8_t> &bytes = image_bytes[i];
         const std::string uri = ji.string_or("uri", "");
+        image_uri[i] = uri;
         if (!uri.empty()) {
             bytes = load_uri(uri, base_dir);
         } else {
@@ -304,12 +341,19 @@ void load_gltf(const std::string &filename, int width, int height, int samples, 
             if (off + len > buf.size()) throw std::runtime_error("[tinygltf] image bufferView out of range");
             bytes.assign(buf.begin() + (ptrdiff_t) off, buf.begin() + (ptrdiff_t) (off + len));
         }
-        HostTexture tex;
-        std::string err;
-        if (!decode_image(bytes, tex, err))
-            throw std::runtime_error("[tinygltf] Failed to load image " + std::to_string(i) + " (" + uri + "): " + err);
-        scene.textures.push_back(std::move(tex));
     }
+    // decoding is the largest host cost of a textured scene (Sponza: 69 PNGs, 17 s on one thread): one image per thread
+    scene.textures.resize(jimages.size());
+    std::vector<std::string> image_err(jimages.size());
+#pragma omp parallel for schedule(dynamic, 1)
+    for (long long i = 0; i < (long long) jimages.size(); ++i) {
+        std::string err;
+        if (!decode_image(image_bytes[(size_t) i], scene.textures[(size_t) i], err)) image_err[(size_t) i] = err.empty() ? "decode failed" : err;
+        std::vector<uint8_t>().swap(image_bytes[(size_t) i]);
+    }
+    for (size_t i = 0; i < jimages.size(); ++i)   // the first failing image is reported, as a sequential loader would
+        if (!image_err[i].empty())
+            throw std::runtime_error("[tinygltf] Failed to load image " + std::to_string(i) + " (" + image_uri[i] + "): " + image_err[i]);
 
     // ---- meshes: one Mesh per glTF primitive, in node order (scene_parser.cpp:144-346)
     const Json &jmeshes = arr("meshes"), &jmaterials = arr("materials"), &jtextures = arr("textures");
@@ -326,6 +370,13 @@ void load_gltf(const std::string &filename, int width, int height, int samples, 
         v.count = (size_t) a.number_or("count", 0);
         v.component_type = a.int_or("componentType", 0);
         v.type = a.string_or("type", "");
+        // (beyond the reference, which assumes tightly packed views: scene_parser.cpp:209-262 index the raw pointers)
+        const size_t comps = v.type == "SCALAR" ? 1 : v.type == "VEC2" ? 2 : v.type == "VEC3" ? 3 : v.type == "VEC4" ? 4 : 0;
+        const size_t csize = (v.component_type == 5120 || v.component_type == 5121) ? 1 : (v.component_type == 5122 || v.component_type == 5123) ? 2 : 4;
+        const size_t packed = comps * csize;
+        const size_t bs = (size_t) bv.number_or("byteStride", 0);
+        v.stride = bs ? bs : packed;
+        if (v.count && packed && start + (v.count - 1) * v.stride + packed > buf.size()) throw std::runtime_error("[gltf check] accessor out of range");
         return v;
     };
     auto image_of = [&](const Json *tex_info) -> int {
@@ -412,21 +463,18 @@ void load_gltf(const std::string &filename, int width, int height, int samples, 
             const size_t base = n_tris_total;
             n_tris_total += ntri;
             scene.tris.resize(n_tris_total);
-            const float *pv = (const float *) pos.ptr;
-            const float *nv = (const float *) nrm.ptr;
-            const float *tv = (const float *) uv.ptr;
-            const float *gv = (const float *) tan.ptr;
+            const bool nv = nrm.ptr != nullptr, tv = uv.ptr != nullptr, gv = tan.ptr != nullptr;
             bool tangent_warned = false;
             for (size_t i = 0; i < ntri; ++i) {
                 size_t index[3];
                 for (int v = 0; v < 3; ++v) {
                     if (idx.component_type == kU16) {
                         uint16_t x;
-                        std::memcpy(&x, idx.ptr + (i * 3 + (size_t) v) * 2, 2);
+                        std::memcpy(&x, idx.at(i * 3 + (size_t) v), 2);
                         index[v] = x;
                     } else {
                         uint32_t x;
-                        std::memcpy(&x, idx.ptr + (i * 3 + (size_t) v) * 4, 4);
+                        std::memcpy(&x, idx.at(i * 3 + (size_t) v), 4);
                         index[v] = x;
                     }
                 }
@@ -434,7 +482,7 @@ void load_gltf(const std::string &filename, int width, int height, int samples, 
                 float P[3][4];
                 for (int v = 0; v < 3; ++v) {
                     float in[4];
-                    std::memcpy(in, pv + index[v] * 3, 12);
+                    std::memcpy(in, pos.at(index[v]), 12);
                     in[3] = 1.f;
                     mul_vec4(transform, in, P[v]);
                 }
@@ -446,7 +494,7 @@ void load_gltf(const std::string &filename, int width, int height, int samples, 
                 }
                 for (int v = 0; v < 3; ++v) {
                     float in[4] = {0.f, 0.f, 1.f, 0.f};
-                    if (nv) std::memcpy(in, nv + index[v] * 3, 12);
+                    if (nv) std::memcpy(in, nrm.at(index[v]), 12);
                     in[3] = 0.f;
                     float res[4];
                     mul_vec4(normal_transform, in, res);
@@ -454,9 +502,9 @@ void load_gltf(const std::string &filename, int width, int height, int samples, 
                     for (int k = 0; k < 3; ++k) scene.tris.nrm[t * 9 + (size_t) v * 3 + k] = res[k];
                 }
                 if (tv)
-                    for (int v = 0; v < 3; ++v) std::memcpy(&scene.tris.uv[t * 6 + (size_t) v * 2], tv + index[v] * 2, 8);
+                    for (int v = 0; v < 3; ++v) std::memcpy(&scene.tris.uv[t * 6 + (size_t) v * 2], uv.at(index[v]), 8);
                 if (gv) {
-                    for (int v = 0; v < 3; ++v) std::memcpy(&scene.tris.tan[t * 12 + (size_t) v * 4], gv + index[v] * 4, 16);
+                    for (int v = 0; v < 3; ++v) std::memcpy(&scene.tris.tan[t * 12 + (size_t) v * 4], tan.at(index[v]), 16);
                     const float side = scene.tris.tan[t * 12 + 3];
                     if ((scene.tris.tan[t * 12 + 7] != side || scene.tris.tan[t * 12 + 11] != side) && !tangent_warned) {
                         std::cout << "Warning: tangent.w values differ within triangle" << std::endl;
