@@ -53,6 +53,8 @@ struct rtb_scene {
         if (stage) cudaFree(stage);
         if (wf_state) cudaFree(wf_state);
         for (auto &e : stage_events) cudaEventDestroy(e);
+        if (wf_streams.graph_exec) cudaGraphExecDestroy(wf_streams.graph_exec);
+        if (wf_streams.graph) cudaGraphDestroy(wf_streams.graph);
         if (wf_streams_ok) {
             for (auto &s : wf_streams.stream) cudaStreamDestroy(s);
             for (auto &e : wf_streams.join) cudaEventDestroy(e);
@@ -311,7 +313,7 @@ int rtb_render_device(rtb_scene *scene, const rtb_render_params *p, float *d_acc
         rtb::launch_render(scene->d, L, (cudaStream_t) stream);
         scene->launches += local_rows ? 1 : 0;
     } else {
-        const size_t need = rtb::wf_alloc_bytes(rtb::wf_slots(L), std::max(1, scene->d.ray_depth - 1));
+        const size_t need = rtb::wf_alloc_bytes(rtb::wf_slots(L), std::max(1, scene->d.ray_depth - 1), scene->d.bvh.max_depth);
         if (scene->wf_bytes < need) {
             // the previous state may still be in use by work queued on a caller's stream
             if (scene->wf_state) { RTB_CUDA(cudaDeviceSynchronize()); cudaFree(scene->wf_state); }

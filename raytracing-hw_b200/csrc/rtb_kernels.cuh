@@ -30,15 +30,20 @@ struct RenderLaunch {
 void launch_render(const DScene &sc, const RenderLaunch &p, cudaStream_t stream);
 // wavefront (ray-queue) integrator, rtb_wavefront.cu; `state` = wf_alloc_bytes() bytes of device memory
 unsigned wf_slots(const RenderLaunch &p);
-size_t wf_alloc_bytes(unsigned n_slots, int depth_cap);
+size_t wf_alloc_bytes(unsigned n_slots, int depth_cap, int bvh_depth);
 // stage_events (may be null): filled with events bracketing every k_wf_trace launch, see rtb_scene_stage_ms()
-constexpr int kWfMaxGroups = 8;
+constexpr int kWfMaxGroups = 16;
 struct WfStreams {   // owned by the scene: one stream per slot group + fork / join events (null: one group, caller's stream)
     cudaStream_t stream[kWfMaxGroups];
     cudaEvent_t fork, join[kWfMaxGroups];
+    // the captured block of iterations (see launch_render_wavefront) and the launch parameters it was captured for
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t graph_exec = nullptr;
+    std::vector<unsigned char> graph_key;
+    unsigned long long graph_launches = 0;   // kernels per replay
 };
 void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *state, cudaStream_t stream, unsigned long long *launches,
-                             std::vector<cudaEvent_t> *stage_events, const WfStreams *aux);
+                             std::vector<cudaEvent_t> *stage_events, WfStreams *aux);
 void launch_resolve(const float *d_accum, size_t n_pixels, int samples, uint8_t *d_rgb8, cudaStream_t stream);
 
 }  // namespace rtb

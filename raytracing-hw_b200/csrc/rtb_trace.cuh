@@ -87,6 +87,29 @@ struct LaneTraversal {
         best.u = u2f((uint32_t) uv.x);
         best.v = u2f((uint32_t) uv.y);
     }
+    // ---- suspending a ray (form 3): everything a later launch needs to carry on from exactly this state.  The ray
+    // itself is re-made from the caller's ray record (make_ray is a pure function of it).  rec: kSuspHeader + sp entries.
+    static constexpr int kSuspHeader = 5;
+    RTB_HD void save3(int2 *rec) const {
+        rec[0] = make_int2(link, sp);
+        rec[1] = make_int2(tri_i, tri_end);
+        rec[2] = make_int2((int) f2u(best.t), best.id);
+        rec[3] = make_int2((int) f2u(cull), 0);
+        rec[4] = s2[kUvSlot];
+        for (int i = 0; i < sp; ++i) rec[kSuspHeader + i] = s2[i];
+    }
+    // `r` has been set (as for begin)
+    RTB_HD void load3(const int2 *rec) {
+        const int2 a = rec[0], b = rec[1], c = rec[2], d = rec[3];
+        link = a.x; sp = a.y;
+        tri_i = b.x; tri_end = b.y;
+        best.t = u2f((uint32_t) c.x); best.id = c.y;
+        cull = u2f((uint32_t) d.x);
+        s2[kUvSlot] = rec[4];
+        for (int i = 0; i < sp; ++i) s2[i] = rec[kSuspHeader + i];
+        omax = ray_omax(r);
+        sgn = (r.d[0] > 0.f ? 1u : 0u) | (r.d[1] > 0.f ? 2u : 0u) | (r.d[2] > 0.f ? 4u : 0u);
+    }
     RTB_HD bool wants_node() const { return link >= 0; }
     RTB_HD bool wants_tri() const { return tri_i < tri_end; }
     RTB_HD bool wants_pop() const { return link == kPopLink; }
@@ -275,8 +298,19 @@ __device__ __forceinline__ void ldg256(const float4 *p, float4 &lo, int4 &hi) {
 //   between two refill votes.  See DESIGN.md for the ncu evidence and for what was tried and dropped (parked leaves,
 //   batching the triangle code, a separate instantiation for rays without zero direction components: each cost more
 //   in registers -- occupancy -- than it saved in instructions).
-template <bool COUNT, int MODE, class Fetch, class Emit>
-__device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsigned *queue_head, Fetch fetch, Emit emit, QueueCounters *cnt, const TracePolicy pol) {
+//
+// Fetch(idx, L, tag&) loads queue entry idx into L.r and returns 0 (the entry holds no ray), 1 (a new ray: L.begin
+// follows) or 2 (a ray suspended by an earlier launch: Fetch has restored the traversal state with L.load3).
+// Suspend(tag, L): see `tail_steps`.
+//
+// tail_steps > 0 (form 3 only) bounds the TAIL of a launch: a ray that has run tail_steps steps in this launch while the
+// queue is already empty is suspended -- Suspend() saves its traversal state (L.save3) and the lane retires -- and a
+// later launch resumes it where it stopped.  Without this a launch lasts as long as its longest ray (hundreds of
+// steps against a mean of ~50), which is what bounds small frames / many GPUs (profiles/r01k_*): the iterations of a
+// pixel are a dependent chain.  The ray's visits, arithmetic and result are unchanged; only when they happen moves.
+template <bool COUNT, int MODE, class Fetch, class Emit, class Suspend>
+__device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsigned *queue_head, Fetch fetch, Emit emit, Suspend suspend,
+                                                 const int tail_steps, QueueCounters *cnt, const TracePolicy pol) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     __align__(8) int2 stack[LaneTraversal<COUNT>::kStack3];
@@ -285,6 +319,7 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
     else L.reset(reinterpret_cast<int *>(stack), reinterpret_cast<float *>(stack) + kMaxStack + 1);
     unsigned tag = 0;
     bool have_ray = false, exhausted = false;
+    int budget = tail_steps;
 
     while (true) {
         const bool wantR = L.finished() && !exhausted;
@@ -305,11 +340,13 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
                 }
                 const unsigned idx = base + (unsigned) __popc(mR & ((1u << lane) - 1u));
                 if (idx < n) {
-                    have_ray = fetch(idx, L.r, tag);
-                    if (have_ray) {
+                    const int got = fetch(idx, L, tag);
+                    have_ray = got != 0;
+                    if (got == 1) {
                         cnt->rays += 1;
                         L.begin(b, cnt);
                     }
+                    budget = tail_steps;
                 } else {
                     have_ray = false;
                     exhausted = true;
@@ -346,6 +383,21 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
             ldg256(p + 2, c, d);
             if (doN) L.node_compute3(a, bb, c, d, cnt);
             if (doL) L.tri_compute3(a, bb, c, cnt);
+            }
+            if (tail_steps > 0) {
+                budget -= MODE - 2;
+                if (budget <= 0 && !L.finished()) {
+                    // this ray has had its steps: if the queue has run dry the launch is in its tail -- step aside
+                    if (*reinterpret_cast<volatile unsigned *>(queue_head) >= n) {
+                        suspend(tag, L);
+                        have_ray = false;
+                        L.link = kDoneLink;
+                        L.sp = 1;
+                        L.tri_i = L.tri_end = 0;
+                    } else {
+                        budget = 16;
+                    }
+                }
             }
         } else {
 #pragma unroll

@@ -24,6 +24,7 @@ namespace {
 constexpr int kShadeBlock = 128;
 constexpr int kDefaultShadeBlocks = 6;   // CTAs per SM the shade kernel is compiled for (RTB_SHADE_BLOCKS: 5, 6, 8)
 constexpr int kCompactBlock = 1024;
+constexpr int kDefaultTailSteps = 96;      // see trace_persistent (RTB_TRACE_TAIL; 0 = rays are never suspended)
 constexpr int kDefaultRaysPerLane = 1;   // k_wf_trace keeps ceil(active / (128 * this)) CTAs (RTB_TRACE_RPL)
 
 // slots [slot_begin, slot_begin + count) of one slot group; list / n_list / queue_head are the group's own
@@ -39,26 +40,41 @@ __global__ void __launch_bounds__(256) k_wf_init(const __grid_constant__ DScene 
 }
 
 template <bool COUNT, int MINB, int MODE>
-__global__ void __launch_bounds__(128, MINB) k_wf_trace(const __grid_constant__ DScene sc, const WfState w, const unsigned *__restrict__ list,
+__global__ void __launch_bounds__(128, MINB) k_wf_trace(const __grid_constant__ DScene sc, const WfState w, unsigned *list,
                                                   const unsigned *__restrict__ n_list, unsigned *__restrict__ queue_head,
                                                   unsigned long long *__restrict__ counters, const TracePolicy pol,
-                                                  const unsigned rays_per_lane) {
+                                                  const unsigned rays_per_lane, const int tail_steps) {
     const unsigned n = *n_list;
     // the grid was sized on the host for the list's capacity; when few slots are still active, the surplus CTAs leave
     // at once so that every remaining lane still pulls several rays from the queue (dynamic balance needs that)
     if (n == 0 || (blockIdx.x > 0 && blockIdx.x * (128u * rays_per_lane) >= n)) return;
     QueueCounters cnt = {0ull, 0ull, 0u};
+    // the tag of a ray is its index in the active list: the entry says which slot it is and whether it was suspended
     trace_persistent<COUNT, MODE>(
         sc.bvh, n, queue_head,
-        [&](unsigned i, Ray &r, unsigned &tag) {
+        [&](unsigned i, LaneTraversal<COUNT> &L, unsigned &tag) {
             const unsigned e = list[i];
-            if (e & kSlotDone) return false;
-            tag = e;
-            wf_load_ray(w, e, r);
-            return true;
+            if (e & kSlotDone) return 0;
+            tag = i;
+            const unsigned slot = e & kSlotIndex;
+            wf_load_ray(w, slot, L.r);
+            if (MODE >= 3 && (e & kSlotSuspended)) {
+                L.load3(w.susp + (size_t) slot * w.susp_stride);
+                return 2;
+            }
+            return 1;
         },
-        [&](unsigned slot, const Ray &, const Hit &h) { w.hit[slot] = make_float4(h.t, h.u, h.v, u2f((uint32_t) h.id)); },
-        &cnt, pol);
+        [&](unsigned i, const Ray &, const Hit &h) {
+            const unsigned e = list[i];
+            w.hit[e & kSlotIndex] = make_float4(h.t, h.u, h.v, u2f((uint32_t) h.id));
+            if (e & kSlotSuspended) list[i] = e & ~kSlotSuspended;
+        },
+        [&](unsigned i, const LaneTraversal<COUNT> &L) {
+            const unsigned e = list[i];
+            L.save3(w.susp + (size_t) (e & kSlotIndex) * w.susp_stride);
+            if (!(e & kSlotSuspended)) list[i] = e | kSlotSuspended;
+        },
+        MODE >= 3 ? tail_steps : 0, &cnt, pol);
     if (counters) {
         for (int o = 16; o > 0; o >>= 1) {
             cnt.rays += __shfl_down_sync(0xffffffffu, cnt.rays, o);
@@ -86,7 +102,7 @@ __global__ void __launch_bounds__(kShadeBlock, MINB) k_wf_shade(const __grid_con
     PathCounters pc = {0ull, 0ull, {0ull, 0ull}, {0ull, 0ull}};
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const unsigned e = list[i];
-        if (e & kSlotDone) continue;
+        if (e & (kSlotDone | kSlotSuspended)) continue;   // (a suspended ray has no hit yet: the slot waits for a later launch)
         const unsigned ne = wf_shade_slot<COUNT>(sc, p, w, e, &pc);
         if (ne != e) list[i] = ne;
     }
@@ -183,14 +199,16 @@ __global__ void __launch_bounds__(kCompactBlock) k_wf_scatter(const unsigned *__
 }
 }  // namespace
 
-size_t wf_state_bytes(unsigned n_slots, int depth_cap) {
-    const size_t per_slot = 16 + 8 + 16 + 16 + 16 + (size_t) depth_cap * (16 + 16 + 4) + 2 * 4;
+static unsigned wf_susp_stride(int bvh_depth) { return (unsigned) (LaneTraversal<false>::kSuspHeader + std::max(0, bvh_depth) + 2); }
+
+size_t wf_state_bytes(unsigned n_slots, int depth_cap, int bvh_depth) {
+    const size_t per_slot = 16 + 8 + 16 + 16 + 16 + (size_t) depth_cap * (16 + 16 + 4) + 2 * 4 + (size_t) wf_susp_stride(bvh_depth) * 8;
     const size_t blocks = ((size_t) n_slots + kCompactBlock - 1) / kCompactBlock + kWfMaxGroups;
     return per_slot * n_slots + blocks * 4 + 4096;
 }
 
 // Carves the state arrays out of one allocation (`base`, wf_alloc_bytes() bytes, 256-byte aligned).
-static void wf_carve(char *base, unsigned n_slots, int depth_cap, WfState &w, unsigned *lists[2], unsigned **block_counts, unsigned **scalars) {
+static void wf_carve(char *base, unsigned n_slots, int depth_cap, int bvh_depth, WfState &w, unsigned *lists[2], unsigned **block_counts, unsigned **scalars) {
     size_t off = 0;
     auto take = [&](size_t bytes) {
         char *p = base + off;
@@ -207,15 +225,17 @@ static void wf_carve(char *base, unsigned n_slots, int depth_cap, WfState &w, un
     w.stk_m = (float4 *) take((size_t) n_slots * 16 * depth_cap);
     w.ray_b = (float2 *) take((size_t) n_slots * 8);
     w.stk_a = (float *) take((size_t) n_slots * 4 * depth_cap);
+    w.susp_stride = wf_susp_stride(bvh_depth);
+    w.susp = (int2 *) take((size_t) n_slots * w.susp_stride * 8);
     lists[0] = (unsigned *) take((size_t) n_slots * 4);
     lists[1] = (unsigned *) take((size_t) n_slots * 4);
     *block_counts = (unsigned *) take((((size_t) n_slots + kCompactBlock - 1) / kCompactBlock + kWfMaxGroups) * 4);
     *scalars = (unsigned *) take(256);
 }
 
-size_t wf_alloc_bytes(unsigned n_slots, int depth_cap) {
-    // every array is rounded up to 256 bytes by wf_carve: 12 arrays
-    return wf_state_bytes(n_slots, depth_cap) + 12 * 256;
+size_t wf_alloc_bytes(unsigned n_slots, int depth_cap, int bvh_depth) {
+    // every array is rounded up to 256 bytes by wf_carve: 13 arrays
+    return wf_state_bytes(n_slots, depth_cap, bvh_depth) + 13 * 256;
 }
 
 unsigned wf_slots(const RenderLaunch &p) {
@@ -243,18 +263,18 @@ int wf_groups(unsigned n_slots) {
 // kernel overlap the other group's ALU-bound queue kernel.  With stage timing on, one group on the caller's stream:
 // a kernel's duration is only defined when it runs alone.
 void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *state, cudaStream_t stream, unsigned long long *launches,
-                             std::vector<cudaEvent_t> *stage_events, const WfStreams *aux) {
+                             std::vector<cudaEvent_t> *stage_events, WfStreams *aux) {
     if (p.local_rows <= 0 || p.width <= 0 || p.samples <= 0) return;
     const unsigned n_slots = wf_slots(p);
     const int depth_cap = std::max(1, sc.ray_depth - 1);
     WfState w;
     unsigned *lists[2], *block_counts, *scalars;
-    wf_carve((char *) state, n_slots, depth_cap, w, lists, &block_counts, &scalars);
+    wf_carve((char *) state, n_slots, depth_cap, sc.bvh.max_depth, w, lists, &block_counts, &scalars);
     unsigned long long nl = 0;
 
     // a group needs enough slots to fill the persistent queue kernel a few times over
     int G = (stage_events || !aux) ? 1 : wf_groups(n_slots);
-    while (G > 1 && n_slots / (unsigned) G < 32u * 1024u) --G;
+    while (G > 1 && n_slots / (unsigned) G < 16u * 1024u) --G;
     struct Group {
         unsigned begin, count, n_blocks, block_off;
         unsigned *lists[2], *n_list[2], *queue_head;
@@ -317,7 +337,18 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
         if (const char *e = std::getenv("RTB_TRACE_RPL")) v = std::max(1, std::atoi(e));
         return (unsigned) v;
     }();
-    const long long iterations = (long long) p.samples * sc.ray_depth;
+    // RTB_TRACE_TAIL: steps a ray may run in one launch once the queue is empty before it is suspended (0: never)
+    static const int tail_steps_env = [] {
+        int v = kDefaultTailSteps;
+        if (const char *e = std::getenv("RTB_TRACE_TAIL")) v = std::max(0, std::atoi(e));
+        return v;
+    }();
+    const int tail_steps = (mode >= 3 && !p.count_tests) ? tail_steps_env : 0;
+    // samples x ray_depth iterations trace every ray a pixel can need when no ray is ever suspended; with suspension a
+    // slot sometimes spends an iteration without finishing its ray, so a margin is enqueued up front and the live counts
+    // are then read back (the one host synchronisation of a frame) until every group's list is empty
+    const long long base_iterations = (long long) p.samples * sc.ray_depth;
+    const long long iterations = tail_steps > 0 ? base_iterations + base_iterations / 16 + 8 : base_iterations;
     const int period = 16;   // iterations between compactions
     // optional stage timing: events[2*it], events[2*it+1] bracket iteration it's k_wf_trace; events[2*iterations] ends the frame
     size_t ev_i = 0;
@@ -330,12 +361,12 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
         }
         cudaEventRecord((*stage_events)[ev_i++], stream);
     };
-    for (long long it = 0; it < iterations; ++it) {
+    auto run_iteration = [&](long long it) {
         for (int g = 0; g < G; ++g) {
             Group &q = grp[g];
             unsigned *list = q.lists[q.cur], *n_list = q.n_list[q.cur];
             mark();
-#define RTB_LAUNCH_T(COUNT, MINB, MODE) k_wf_trace<COUNT, MINB, MODE><<<q.trace_grid, 128, 0, q.st>>>(sc, w, list, n_list, q.queue_head, p.d_counters, pol, rays_per_lane)
+#define RTB_LAUNCH_T(COUNT, MINB, MODE) k_wf_trace<COUNT, MINB, MODE><<<q.trace_grid, 128, 0, q.st>>>(sc, w, list, n_list, q.queue_head, p.d_counters, pol, rays_per_lane, tail_steps)
 #define RTB_LAUNCH_TM(MODE)                                          \
             if (p.count_tests) RTB_LAUNCH_T(true, 10, MODE);         \
             else if (bps <= 9) RTB_LAUNCH_T(false, 9, MODE);         \
@@ -352,14 +383,101 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
             nl += 2;
             if ((it + 1) % period == 0 && it + 1 < iterations) compact(q);
         }
-    }
-    mark();
-    if (G > 1) {   // join
+    };
+    // The groups' iterations are many short launches (1/8 of a 1080p frame in 8 groups: 20 k launches per 64 spp, and
+    // the host thread tops out at ~3 us per launch: profiles/r01k_groups_sweep.txt).  So 32 iterations -- two compaction
+    // periods, after which every group's list pointers are back where they started -- are captured ONCE into a CUDA
+    // graph (the groups' streams fork from and join the caller's stream inside the capture) and replayed; what is left
+    // over is launched directly.  Every kernel reads its live list length from device memory, so a replay is valid.
+    long long it0 = 0;
+    static const bool graphs_on = [] { const char *e = std::getenv("RTB_WF_GRAPH"); return !(e && std::atoi(e) == 0); }();
+    const long long kBlockIts = 2 * period;
+    const long long n_graph_blocks = (G > 1 && !stage_events && graphs_on && iterations > 2 * kBlockIts) ? (iterations - 1) / kBlockIts : 0;
+    if (n_graph_blocks > 0) {
+        // everything queued on the groups' streams so far (init + first compaction) must precede the first replay
         for (int g = 0; g < G; ++g) {
             cudaEventRecord(aux->join[g], grp[g].st);
             cudaStreamWaitEvent(stream, aux->join[g], 0);
         }
+        // the block depends on nothing but the launch parameters: keep it across frames
+        std::vector<unsigned char> key;
+        auto add = [&](const void *ptr, size_t bytes) { key.insert(key.end(), (const unsigned char *) ptr, (const unsigned char *) ptr + bytes); };
+        add(&sc, sizeof sc); add(&p, sizeof p); add(&state, sizeof state); add(&G, sizeof G); add(&mode, sizeof mode);
+        add(&bps, sizeof bps); add(&tail_steps, sizeof tail_steps); add(&shade_bps, sizeof shade_bps); add(&rays_per_lane, sizeof rays_per_lane); add(&pol, sizeof pol);
+        bool ok = true;
+        if (!aux->graph_exec || key != aux->graph_key) {
+            if (aux->graph_exec) { cudaStreamSynchronize(stream); cudaGraphExecDestroy(aux->graph_exec); aux->graph_exec = nullptr; }
+            if (aux->graph) { cudaGraphDestroy(aux->graph); aux->graph = nullptr; }
+            const unsigned long long nl_before = nl;
+            int cur_before[kWfMaxGroups];
+            for (int g = 0; g < G; ++g) cur_before[g] = grp[g].cur;
+            ok = cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+            if (ok) {
+                cudaEventRecord(aux->fork, stream);
+                for (int g = 0; g < G; ++g) cudaStreamWaitEvent(grp[g].st, aux->fork, 0);
+                for (long long it = 0; it < kBlockIts; ++it) run_iteration(it);   // (it + 1 < iterations holds: see n_graph_blocks)
+                for (int g = 0; g < G; ++g) {
+                    cudaEventRecord(aux->join[g], grp[g].st);
+                    cudaStreamWaitEvent(stream, aux->join[g], 0);
+                }
+                ok = cudaStreamEndCapture(stream, &aux->graph) == cudaSuccess && aux->graph != nullptr;
+            }
+            if (ok) ok = cudaGraphInstantiate(&aux->graph_exec, aux->graph, 0) == cudaSuccess;
+            aux->graph_launches = nl - nl_before;
+            nl = nl_before;
+            for (int g = 0; g < G; ++g) grp[g].cur = cur_before[g];   // (a whole block leaves them unchanged anyway)
+            if (ok) {
+                aux->graph_key.swap(key);
+            } else {
+                cudaGetLastError();   // capture / instantiation unavailable: everything is launched directly below
+                if (aux->graph_exec) { cudaGraphExecDestroy(aux->graph_exec); aux->graph_exec = nullptr; }
+                if (aux->graph) { cudaGraphDestroy(aux->graph); aux->graph = nullptr; }
+                aux->graph_key.clear();
+            }
+        }
+        if (ok) {
+            long long done = 0;
+            for (; done < n_graph_blocks; ++done)
+                if (cudaGraphLaunch(aux->graph_exec, stream) != cudaSuccess) { cudaGetLastError(); break; }
+            nl += aux->graph_launches * (unsigned long long) done;
+            it0 = done * kBlockIts;
+        }
+        // the directly launched rest follows the replays
+        cudaEventRecord(aux->fork, stream);
+        for (int g = 0; g < G; ++g) cudaStreamWaitEvent(grp[g].st, aux->fork, 0);
     }
+    for (long long it = it0; it < iterations; ++it) run_iteration(it);
+    auto join = [&]() {
+        if (G <= 1) return;
+        for (int g = 0; g < G; ++g) {
+            cudaEventRecord(aux->join[g], grp[g].st);
+            cudaStreamWaitEvent(stream, aux->join[g], 0);
+        }
+    };
+    if (tail_steps > 0) {
+        // Suspended rays cost their slots extra iterations: compact (that counts the live slots), read the counts back,
+        // and go on in rounds of 16 until every list is empty.  The margin above makes one read-back the normal case.
+        long long it = iterations;
+        for (int round = 0; round < 4096; ++round) {
+            unsigned live[kWfMaxGroups];
+            for (int g = 0; g < G; ++g) {
+                compact(grp[g]);
+                cudaMemcpyAsync(&live[g], grp[g].n_list[grp[g].cur], sizeof(unsigned), cudaMemcpyDeviceToHost, grp[g].st);
+            }
+            join();
+            if (cudaStreamSynchronize(stream) != cudaSuccess) break;   // (the caller sees the error)
+            unsigned total = 0;
+            for (int g = 0; g < G; ++g) total += live[g];
+            if (total == 0) break;
+            if (G > 1) {
+                cudaEventRecord(aux->fork, stream);
+                for (int g = 0; g < G; ++g) cudaStreamWaitEvent(grp[g].st, aux->fork, 0);
+            }
+            for (int k = 0; k < 16; ++k) run_iteration(it++);
+        }
+    }
+    mark();
+    join();
     if (stage_events) stage_events->resize(ev_i);   // (events beyond ev_i were created by an earlier, longer frame)
     if (launches) *launches += nl;
 }

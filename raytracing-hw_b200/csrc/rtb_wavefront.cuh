@@ -19,6 +19,8 @@
 namespace rtb {
 
 constexpr unsigned kSlotDone = 0x80000000u;   // high bit of an active-list entry: the slot has finished all samples
+constexpr unsigned kSlotSuspended = 0x40000000u;   // the slot's ray was suspended by the queue kernel (rtb_trace.cuh: tail_steps): no hit yet, the shade step skips it
+constexpr unsigned kSlotIndex = 0x3FFFFFFFu;
 constexpr int kWfTileW = 8, kWfTileH = 4;     // a group of 32 consecutive slots is an 8x4 pixel tile
 
 // Path state, SoA over slots (180 GB of HBM: ~0.3 kB per pixel is nothing; 1080p = 0.6 GB)
@@ -34,6 +36,8 @@ struct WfState {
     float4 *stk_e;           // [depth_cap][n_slots] emission.xyz, 1/pdf          (struct Bounce, rtb_shade.cuh)
     float4 *stk_m;           // [depth_cap][n_slots] material.xyz, cosine
     float *stk_a;            // [depth_cap][n_slots] material alpha
+    int2 *susp;              // [n_slots][susp_stride] traversal state of a suspended ray (LaneTraversal::save3)
+    unsigned susp_stride;    // kSuspHeader + BVH depth + 2 entries
 };
 
 RTB_HD bool wf_slot_pixel(const RenderLaunch &p, unsigned slot, int &px, int &lr, int &py) {
@@ -203,6 +207,6 @@ RTB_HD unsigned wf_shade_slot(const DScene &sc, const RenderLaunch &p, const WfS
 }
 
 // ---- launchers (rtb_wavefront.cu)
-size_t wf_state_bytes(unsigned n_slots, int depth_cap);
+size_t wf_state_bytes(unsigned n_slots, int depth_cap, int bvh_depth);
 
 }  // namespace rtb

@@ -96,12 +96,33 @@ int devsim_closest_hit_lane(const rtb_scene_desc *desc, const float *rays6, size
         int2 stack2[LaneTraversal<true>::kStack3];
         LaneTraversal<true> L;
         L.reset(stack_link, stack_m);
-        if (schedule_seed == 3u) L.reset3(stack2);
+        if (schedule_seed >= 3u) L.reset3(stack2);
         make_ray(L.r, rays6[i * 6], rays6[i * 6 + 1], rays6[i * 6 + 2], rays6[i * 6 + 3], rays6[i * 6 + 4], rays6[i * 6 + 5]);
         Counters c = {0, 0};
         L.begin(s.d.bvh, &c);
         // schedule_seed selects the form of the state machine: 3 = one pop / decode site per step (MODE 3), else the first form
         if (schedule_seed == 3u) { while (!L.finished()) L.step3(s.d.bvh, &c); L.finish3(); }
+        else if (schedule_seed >= 100u) {
+            // form 3, suspended every (schedule_seed - 100) steps: the state goes through save3 / load3 into a FRESH lane
+            // (new stack, ray re-made from the ray record), as the queue kernel does across launches
+            const int every = (int) (schedule_seed - 100u);
+            int2 rec[LaneTraversal<true>::kSuspHeader + kMaxStack + 2];
+            int2 stack3[LaneTraversal<true>::kStack3];
+            int left = every;
+            while (!L.finished()) {
+                L.step3(s.d.bvh, &c);
+                if (--left <= 0 && !L.finished()) {
+                    L.save3(rec);
+                    LaneTraversal<true> M;
+                    M.reset3(L.s2 == stack2 ? stack3 : stack2);
+                    make_ray(M.r, rays6[i * 6], rays6[i * 6 + 1], rays6[i * 6 + 2], rays6[i * 6 + 3], rays6[i * 6 + 4], rays6[i * 6 + 5]);
+                    M.load3(rec);
+                    L = M;
+                    left = every;
+                }
+            }
+            L.finish3();
+        }
         else while (!L.finished()) L.step(s.d.bvh, &c);
         box += c.box;
         tri += c.tri;

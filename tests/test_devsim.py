@@ -59,6 +59,21 @@ def test_lane_form3_equals_first_form(name, host_scene):
 
 
 @pytest.mark.parametrize("name", SCENES)
+@pytest.mark.parametrize("every", [1, 7, 40])
+def test_lane_form3_suspend_resume(name, every, host_scene):
+    """a ray suspended every `every` steps and resumed in a fresh lane (LaneTraversal::save3 / load3: what the queue kernel
+    does with the tail of a launch) performs the same tests and gives the same answer as the uninterrupted ray"""
+    g = _util.load_golden(name)
+    hs = host_scene(name)
+    rays = np.concatenate([_util.box_rays(g["root_box"], 4096, seed=1000), _util.edge_rays(hs, g["root_box"], 4096, seed=78)])
+    whole = _util.devsim_closest_hit_lane(hs, rays, 3)
+    cut = _util.devsim_closest_hit_lane(hs, rays, 100 + every)
+    assert (cut["box_tests"], cut["tri_tests"]) == (whole["box_tests"], whole["tri_tests"])
+    for k in ("id", "t", "u", "v"):
+        assert np.array_equal(cut[k], whole[k]), k
+
+
+@pytest.mark.parametrize("name", SCENES)
 def test_lane_form3_on_decision_boundaries(name, host_scene):
     """rays that sit on the box test's decision boundaries (zero direction components, origins on box planes, rays
     through box corners): form 3 vs the twin (the pinned restatement of the reference's recursion)"""
