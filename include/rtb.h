@@ -190,7 +190,9 @@ int rtb_light_pdf(rtb_scene *scene, const float *rays6, size_t n, float *pdf);
  * rgb8  (may be NULL): (row_end-row_begin) x width x 3 bytes after x(1/samples), ACES, gamma 1/2.2, round.
  * HOST pointers; the device->host copy is inside the call.                                                         */
 int rtb_render(rtb_scene *scene, const rtb_render_params *params, float *accum, uint8_t *rgb8, rtb_stats *stats);
-/* same, DEVICE output pointers, asynchronous on `stream`; d_counters: 6 uint64 {rays, light queries, box, tri,
+/* same, DEVICE output pointers, enqueued on `stream`.  The ray-queue integrator reads its live-slot counts back before it
+ * returns (one short stream synchronisation per frame); RTB_TRACE_TAIL=0 or the megakernel flag
+ * keep the call fully asynchronous.  d_counters: 6 uint64 {rays, light queries, box, tri,
  * light-query box, light-query tri} or NULL (box / tri are totals over both BVHs and need RTB_RENDER_COUNTERS)    */
 int rtb_render_device(rtb_scene *scene, const rtb_render_params *params, float *d_accum, uint8_t *d_rgb8,
                       unsigned long long *d_counters, void *stream);
