@@ -141,3 +141,30 @@ def test_full_size_properties():
     assert 0.90 < total_hits / (chunk * n_chunks) < 0.93       # ~92 % hit rate
     want = _util.twin_bvh(hs).closest_hit(first[0])
     assert np.array_equal(first[1], want["id"]) and np.array_equal(first[2], want["t"])
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_decision_boundary_rays(name, host_scene):
+    """rays ON the box test's decision boundaries (zero direction components, origins on box planes, rays through box
+    corners; tests/_util.py: edge_rays): the queue kernel (form 3: box_test_z, one pop / decode site, 256-bit loads)
+    against the in-order global-best traversal of the same arithmetic -- every bit -- and against the reference's
+    recursion (twin): same hit / miss, equal t,u,v where the ids agree, the rest are the documented tie case"""
+    g = _util.load_golden(name)
+    hs = host_scene(name)
+    rays = _util.edge_rays(hs, g["root_box"], 200_000, seed=79)
+    got = rtb.Scene(hs, 0).closest_hit(rays, cull=rtb.CULL_GLOBAL)
+    first = _util.devsim_closest_hit_lane(hs, rays, 0)
+    for k in ("id", "t", "u", "v"):
+        assert np.array_equal(got[k], first[k]), k
+    want = _util.twin_bvh(hs).closest_hit(rays)
+    assert np.array_equal(got["id"] >= 0, want["id"] >= 0)
+    same = got["id"] == want["id"]
+    hit = want["id"] >= 0
+    for k in ("t", "u", "v", "inside"):
+        assert np.array_equal(got[k][hit & same], want[k][hit & same]), k
+    tie = hit & ~same
+    assert np.count_nonzero(tie) <= 0.005 * rays.shape[0]
+    assert np.all(got["t"][tie] <= want["t"][tie])
+    ref = rtb.Scene(hs, 0).closest_hit(rays, cull=rtb.CULL_REFERENCE)
+    for k in ("id", "t", "u", "v", "inside"):
+        assert np.array_equal(ref[k], want[k]), k

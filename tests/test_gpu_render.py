@@ -173,3 +173,14 @@ def test_full_size_properties(host_scene):
     assert np.array_equal(a["rgb"][::16], twin.resolve(a["accum"][::16], S))
     rays = a["stats"]["closest_hit_rays"]
     assert W * H * S <= rays <= 6 * W * H * S
+
+
+def test_tail_suspension_groups_and_graph_replay_keep_every_bit():
+    """the queue kernel suspending the tail rays of a launch (RTB_TRACE_TAIL), the slot groups on their own streams and
+    the CUDA-graph replay of their iterations only change WHEN a ray is traced: the frame's sums and bytes equal those
+    of one group, direct launches, no suspension.  The switches are read once per process, so each variant renders in
+    its own process (tools/check_graph_replay.py); 640x360 x 24 spp = 144 iterations over 8 groups."""
+    tool = os.path.join(_util.ROOT, "tools", "check_graph_replay.py")
+    r = subprocess.run([os.sys.executable, tool, "sponza_small", "640", "360", "24"], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert "graph replay == direct launches: True" in r.stdout
