@@ -323,6 +323,12 @@ def roofline(r):
 
 def main():
     args = parse_args()
+    # stdout carries exactly ONE line, the JSON: libraries that write to file descriptor 1 themselves (NCCL prints
+    # "NCCL version ..." there when the box sets NCCL_DEBUG=VERSION) are sent to stderr; our line goes to the real stdout
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real_stdout
     if args.impl == "reference":
         run_reference_arm(args)
         return
