@@ -243,9 +243,13 @@ unsigned wf_slots(const RenderLaunch &p) {
     return (unsigned) (tiles * 32);
 }
 
-// Measured on one B200 (Sponza stand-in, 64 spp; gpurun_out of run 14): 2.07 M slots -> 1 or 2 groups are best (4: -5 %,
-// 8: -13 %); 0.26 M slots (one GPU's share of a 1080p frame on 8 GPUs) -> 144 / 128 / 117 / 112 ms with 1 / 2 / 4 / 8
-// groups.  Default: as many groups as it takes to bring a group down to ~0.26 M slots.
+// Measured on one B200 (Sponza stand-in, 64 spp, tail suspension on; profiles/r01k_groups_canvas_sweep.txt), Mpix*spp/s:
+//   1/2 of a 1080p frame (1.04 M slots): 268 / 258 / 234 with 1 / 2 / 4 groups
+//   1/4 (0.52 M slots)                 : 234 / 218 / 216 / 216 with 1 / 2 / 4 / 8 groups
+//   1/8 (0.26 M slots)                 : 182 / 194 / 200 / 202 with 2 / 4 / 6 / 8 groups
+// (before rays could be suspended, groups paid off from 1/2 frame down: they hid the tails of each other's launches;
+// with bounded tails their contention costs more than that until a launch is too small to fill the GPU.)
+// Default: one group down to 0.4 M slots, below that as many groups as bring a group down to ~0.26 M / 8 slots.
 int wf_groups(unsigned n_slots) {
     static const int forced = [] {
         int g = 0;
@@ -253,8 +257,9 @@ int wf_groups(unsigned n_slots) {
         return g;
     }();
     if (forced) return forced;
+    if (n_slots >= 400000u) return 1;
     const unsigned g = ((2u << 20) + n_slots / 2) / std::max(1u, n_slots);
-    return (int) std::max(1u, std::min((unsigned) kWfMaxGroups, g));
+    return (int) std::max(1u, std::min(8u, g));
 }
 
 // Slot groups.  The slots are cut into up to kWfMaxGroups contiguous groups, each with its own active list, queue
