@@ -119,7 +119,7 @@ TracePolicy trace_policy() {
 int trace_mode() {
     static int v = [] {
         int m = kDefaultTraceMode;
-        if (const char *e = std::getenv("RTB_TRACE_MODE")) m = std::max(0, std::min(5, std::atoi(e)));
+        if (const char *e = std::getenv("RTB_TRACE_MODE")) m = std::max(3, std::min(5, std::atoi(e)));
         return m;
     }();
     return v;
@@ -128,7 +128,7 @@ int trace_mode() {
 int persistent_blocks_per_sm() {
     static int v = [] {
         int b = kDefaultTraceBlocks;
-        if (const char *e = std::getenv("RTB_TRACE_BLOCKS")) b = std::max(1, std::min(12, std::atoi(e)));
+        if (const char *e = std::getenv("RTB_TRACE_BLOCKS")) b = std::max(1, std::min(10, std::atoi(e)));
         return b;
     }();
     return v;
@@ -158,9 +158,8 @@ void launch_closest_hit(const DScene &sc, const float *d_rays6, size_t n, int cu
 #define RTB_LAUNCH_QM(MODE)                                  \
         if (d_counters) RTB_LAUNCH_Q(true, 10, MODE);        \
         else if (bps <= 9) RTB_LAUNCH_Q(false, 9, MODE);     \
-        else if (bps <= 10) RTB_LAUNCH_Q(false, 10, MODE);   \
-        else RTB_LAUNCH_Q(false, 12, MODE)
-        if (trace_mode() == 0) { RTB_LAUNCH_QM(0); } else if (trace_mode() == 1) { RTB_LAUNCH_QM(1); } else if (trace_mode() == 4) { RTB_LAUNCH_QM(4); } else if (trace_mode() == 5) { RTB_LAUNCH_QM(5); } else { RTB_LAUNCH_QM(3); }
+        else RTB_LAUNCH_Q(false, 10, MODE)
+        if (trace_mode() == 3) { RTB_LAUNCH_QM(3); } else if (trace_mode() == 5) { RTB_LAUNCH_QM(5); } else { RTB_LAUNCH_QM(4); }
 #undef RTB_LAUNCH_QM
 #undef RTB_LAUNCH_Q
         return;

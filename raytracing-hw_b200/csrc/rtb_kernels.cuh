@@ -8,7 +8,7 @@ namespace rtb {
 void launch_closest_hit(const DScene &sc, const float *d_rays6, size_t n, int cull_mode, int *d_id, float *d_t, float *d_u,
                         float *d_v, uint8_t *d_inside, unsigned long long *d_counters, unsigned *d_queue_head, cudaStream_t stream);
 int persistent_grid(int threads_per_block, int blocks_per_sm);
-constexpr int kDefaultTraceMode = 4;       // rtb_trace.cuh: 0 = voted phases, 1 = unified step, 3 / 4 / 5 = form 3 (one pop / decode site), 1 / 2 / 3 steps per refill vote (RTB_TRACE_MODE)
+constexpr int kDefaultTraceMode = 4;       // rtb_trace.cuh: 3 / 4 / 5 = one / two / three steps per refill vote (RTB_TRACE_MODE)
 int trace_mode();
 constexpr int kDefaultTraceBlocks = 9;    // sweeps: profiles/r01d_closest_hit_blocks_sweep.jsonl (first form), profiles/r01i_mode3_sweep.txt (form 3)
 int persistent_blocks_per_sm();   // CTAs per SM of the persistent queue kernels (RTB_TRACE_BLOCKS overrides)

@@ -5,12 +5,14 @@
 // Two causes: (1) the rays of a warp need very different numbers of steps, so the warp lives as long as its
 // longest ray; (2) lanes in the node phase and lanes in the triangle phase serialise.  Here
 //   * every lane owns one ray at a time and REFILLS itself from a global queue (warp-aggregated atomicAdd) as soon
-//     as its ray is finished -- no tail;
-//   * each warp iteration runs ONE phase chosen by vote over the lanes' wishes (refill / node step / triangle step);
-//     the phase body is predicated, control flow is warp-uniform (__ballot_sync), so lanes wanting the same phase
-//     always execute it together.
-// The per-ray arithmetic is that of rtb_traverse.cuh (same functions), so results are bit-identical to
-// closest_hit_global: same visit order per ray, global-best culling.
+//     as its ray is finished;
+//   * a STEP serves every lane: pops and leaf decodes at the top (one site each, where the warp is converged), one
+//     fetch stage in which a lane loads its 64-byte record -- its node or its triangle -- then the node code for
+//     the lanes holding a node and the triangle code for the lanes holding a triangle, both predicated;
+//   * the tail of a launch is bounded: rays still running long after the queue is empty are suspended and resumed
+//     by the next launch (see trace_persistent).
+// The per-ray arithmetic is that of rtb_traverse.cuh, so results are bit-identical to closest_hit_global: same visit
+// order per ray, global-best culling.
 #pragma once
 #include "rtb_traverse.cuh"
 
@@ -24,10 +26,9 @@ struct QueueCounters {
     unsigned rays;          // per lane and launch
 };
 
-// Phase vote of a warp iteration: refill when at least `refill_min` lanes are idle (or nothing else is runnable);
-// otherwise the node phase when lanes_in_node_phase * w_node >= lanes_in_triangle_phase * w_leaf, else the triangle
-// phase.  A node step costs ~2.5x the instructions of a triangle step, so waiting triangle lanes are cheaper to serve
-// early: the default weights come from the sweep in profiles/ (RTB_TRACE_POLICY="refill,w_node,w_leaf" overrides).
+// A warp refills from the queue when at least `refill_min` of its lanes are idle (or none is busy); the default comes
+// from the sweeps in profiles/ (RTB_TRACE_POLICY="refill,1,1" overrides; the two weights belonged to the first form's
+// phase vote and are no longer read).
 struct TracePolicy {
     int refill_min, w_node, w_leaf;
 };
@@ -287,17 +288,11 @@ __device__ __forceinline__ void ldg256(const float4 *p, float4 &lo, int4 &hi) {
                  : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=r"(hi.x), "=r"(hi.y), "=r"(hi.z), "=r"(hi.w)
                  : "l"(p));
 }
-// Fetch(idx, Ray&, tag&) loads queue entry `idx` (normalising as Ray::Ray does) and returns false when the entry holds
-// no ray (a finished slot of the wavefront integrator); Emit(tag, ray, hit) stores the result of the entry's ray.
-//
-// MODE 0 (voted phases): each warp iteration runs ONE phase chosen by vote (refill / node / triangle).
-// MODE >= 1 (unified step): each step serves EVERY lane: one fetch stage in which a lane loads its node
-//   (4 x LDG.128) or its triangle (3 x LDG.128) through the same instructions, then the node code for the lanes
-//   holding a node and the triangle code for the lanes holding a triangle.  Half the iterations per ray of MODE 0
-//   (a lane never waits for its phase to win a vote), so half the exposed memory latencies; MODE steps are taken
-//   between two refill votes.  See DESIGN.md for the ncu evidence and for what was tried and dropped (parked leaves,
-//   batching the triangle code, a separate instantiation for rays without zero direction components: each cost more
-//   in registers -- occupancy -- than it saved in instructions).
+// The persistent loop of the queue kernels ("form 3", see LaneTraversal::pre3); MODE - 2 steps are taken between two
+// refill votes (MODE 3 / 4 / 5).  Earlier forms -- one phase per warp iteration chosen by vote; the first unified step
+// with the pop and the leaf decode inlined at three sites -- and what was tried and dropped (parked leaves, batching or
+// gating the triangle code, a second instantiation for rays without zero direction components, consolidating the tail
+// through an in-launch requeue) are in DESIGN.md section 5 with their ncu evidence.  Emit(tag, ray, hit) stores a result.
 //
 // Fetch(idx, L, tag&) loads queue entry idx into L.r and returns 0 (the entry holds no ray), 1 (a new ray: L.begin
 // follows) or 2 (a ray suspended by an earlier launch: Fetch has restored the traversal state with L.load3).
@@ -315,8 +310,7 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
     const int lane = threadIdx.x & 31;
     __align__(8) int2 stack[LaneTraversal<COUNT>::kStack3];
     LaneTraversal<COUNT> L;
-    if (MODE >= 3) L.reset3(stack);
-    else L.reset(reinterpret_cast<int *>(stack), reinterpret_cast<float *>(stack) + kMaxStack + 1);
+    L.reset3(stack);
     unsigned tag = 0;
     bool have_ray = false, exhausted = false;
     int budget = tail_steps;
@@ -335,7 +329,7 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
             base = __shfl_sync(FULL, base, leader);
             if (wantR) {
                 if (have_ray) {
-                    if (MODE >= 3) L.finish3();
+                    L.finish3();
                     emit(tag, L.r, L.best);
                 }
                 const unsigned idx = base + (unsigned) __popc(mR & ((1u << lane) - 1u));
@@ -354,21 +348,11 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
             }
             continue;
         }
-        if (MODE == 0) {
-            if (L.wants_pop()) L.pop(b);
-            const bool doN = L.wants_node(), doL = L.wants_tri();
-            const int cN = __popc(__ballot_sync(FULL, doN)), cL = __popc(__ballot_sync(FULL, doL));
-            if (cN * pol.w_node >= cL * pol.w_leaf) {
-                if (doN) L.node_step(b, cnt);
-            } else {
-                if (doL) L.tri_step(b, cnt);
-            }
-        } else if (MODE >= 3) {
-            // MODE 3 / 4 / 5: one / two / three steps per refill vote (profiles/r01j_sched_sweep.txt: two is best, +2 %).
-            // Gating the triangle code on the number of lanes holding a triangle (they wait a step unless >= 4 / 8 / 12
-            // want it) was measured there too and loses 4 / 6 / 10 %: a ray's latency matters more than the issue slots.
+        // MODE 3 / 4 / 5: one / two / three steps per refill vote (profiles/r01j_sched_sweep.txt: two is best, +2 %).
+        // Gating the triangle code on the number of lanes holding a triangle (they wait a step unless >= 4 / 8 / 12
+        // want it) was measured there too and loses 4 / 6 / 10 %: a ray's latency matters more than the issue slots.
 #pragma unroll
-            for (int step = 0; step < MODE - 2; ++step) {
+        for (int step = 0; step < MODE - 2; ++step) {
             L.pre3(b);
             const bool doN = L.link >= 0;
             const bool doL = L.tri_i < L.tri_end;
@@ -383,40 +367,20 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
             ldg256(p + 2, c, d);
             if (doN) L.node_compute3(a, bb, c, d, cnt);
             if (doL) L.tri_compute3(a, bb, c, cnt);
-            }
-            if (tail_steps > 0) {
-                budget -= MODE - 2;
-                if (budget <= 0 && !L.finished()) {
-                    // this ray has had its steps: if the queue has run dry the launch is in its tail -- step aside
-                    if (*reinterpret_cast<volatile unsigned *>(queue_head) >= n) {
-                        suspend(tag, L);
-                        have_ray = false;
-                        L.link = kDoneLink;
-                        L.sp = 1;
-                        L.tri_i = L.tri_end = 0;
-                    } else {
-                        budget = 16;
-                    }
+        }
+        if (tail_steps > 0) {
+            budget -= MODE - 2;
+            if (budget <= 0 && !L.finished()) {
+                // this ray has had its steps: if the queue has run dry the launch is in its tail -- step aside
+                if (*reinterpret_cast<volatile unsigned *>(queue_head) >= n) {
+                    suspend(tag, L);
+                    have_ray = false;
+                    L.link = kDoneLink;
+                    L.sp = 1;
+                    L.tri_i = L.tri_end = 0;
+                } else {
+                    budget = 16;
                 }
-            }
-        } else {
-#pragma unroll
-            for (int step = 0; step < MODE; ++step) {
-                if (L.wants_pop()) L.pop(b);
-                const bool doN = L.wants_node();
-                const bool doL = L.wants_tri();
-                // one fetch stage for both kinds of record
-                const float4 *p = doN ? reinterpret_cast<const float4 *>(b.nodes + L.link) : (b.tris + (size_t) L.tri_i * kTriStride);
-                float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a, c = a;
-                int4 d = make_int4(0, 0, 0, 0);
-                if (doN || doL) {
-                    a = __ldg(p);
-                    bb = __ldg(p + 1);
-                    c = __ldg(p + 2);
-                }
-                if (doN) d = __ldg(reinterpret_cast<const int4 *>(p + 3));
-                if (doN) L.template node_compute<false>(b, a, bb, c, d, cnt);
-                if (doL) L.tri_compute(b, a, bb, c, cnt);
             }
         }
     }

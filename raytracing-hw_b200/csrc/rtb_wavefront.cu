@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(const __grid_constant__ 
             tag = i;
             const unsigned slot = e & kSlotIndex;
             wf_load_ray(w, slot, L.r);
-            if (MODE >= 3 && (e & kSlotSuspended)) {
+            if (e & kSlotSuspended) {
                 L.load3(w.susp + (size_t) slot * w.susp_stride);
                 return 2;
             }
@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(const __grid_constant__ 
             L.save3(w.susp + (size_t) (e & kSlotIndex) * w.susp_stride);
             if (!(e & kSlotSuspended)) list[i] = e | kSlotSuspended;
         },
-        MODE >= 3 ? tail_steps : 0, &cnt, pol);
+        tail_steps, &cnt, pol);
     if (counters) {
         for (int o = 16; o > 0; o >>= 1) {
             cnt.rays += __shfl_down_sync(0xffffffffu, cnt.rays, o);
@@ -348,7 +348,7 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
         if (const char *e = std::getenv("RTB_TRACE_TAIL")) v = std::max(0, std::atoi(e));
         return v;
     }();
-    const int tail_steps = (mode >= 3 && !p.count_tests) ? tail_steps_env : 0;
+    const int tail_steps = p.count_tests ? 0 : tail_steps_env;
     // samples x ray_depth iterations trace every ray a pixel can need when no ray is ever suspended; with suspension a
     // slot sometimes spends an iteration without finishing its ray, so a margin is enqueued up front and the live counts
     // are then read back (the one host synchronisation of a frame) until every group's list is empty
@@ -375,9 +375,8 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
 #define RTB_LAUNCH_TM(MODE)                                          \
             if (p.count_tests) RTB_LAUNCH_T(true, 10, MODE);         \
             else if (bps <= 9) RTB_LAUNCH_T(false, 9, MODE);         \
-            else if (bps <= 10) RTB_LAUNCH_T(false, 10, MODE);       \
-            else RTB_LAUNCH_T(false, 12, MODE)
-            if (mode == 0) { RTB_LAUNCH_TM(0); } else if (mode == 1) { RTB_LAUNCH_TM(1); } else if (mode == 4) { RTB_LAUNCH_TM(4); } else if (mode == 5) { RTB_LAUNCH_TM(5); } else { RTB_LAUNCH_TM(3); }
+            else RTB_LAUNCH_T(false, 10, MODE)
+            if (mode == 3) { RTB_LAUNCH_TM(3); } else if (mode == 5) { RTB_LAUNCH_TM(5); } else { RTB_LAUNCH_TM(4); }
 #undef RTB_LAUNCH_TM
 #undef RTB_LAUNCH_T
             mark();
