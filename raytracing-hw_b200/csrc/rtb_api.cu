@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace rtb {
@@ -73,55 +74,99 @@ namespace {
 
 using namespace rtb;
 
-template <class T>
-int upload(rtb_scene *sc, const std::vector<T> &h, const T **out) {
-    *out = nullptr;
-    if (h.empty()) return RTB_OK;
-    void *p = nullptr;
-    RTB_CUDA(cudaMalloc(&p, h.size() * sizeof(T)));
-    sc->allocs.push_back(p);
-    RTB_CUDA(cudaMemcpy(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
-    sc->upload_bytes += h.size() * sizeof(T);
-    *out = (const T *) p;
-    return RTB_OK;
-}
-
-int upload_bvh(rtb_scene *sc, HostBvhOut &h, DBvh &d, uint32_t n_tris) {
-    int rc;
-    if ((rc = upload(sc, h.nodes, &d.nodes)) != RTB_OK) return rc;
-    if ((rc = upload(sc, h.tris, &d.tris)) != RTB_OK) return rc;
-    if ((rc = upload(sc, h.big, &d.big_leaves)) != RTB_OK) return rc;
-    fill_bvh_scalars(h, d, n_tris);
-    return RTB_OK;
-}
-
-// Several host arrays into ONE device allocation (256-byte aligned pieces), so that a single L2 access-policy window
-// can cover them.
-struct Piece {
-    const void *src;
-    size_t bytes;
-    const void **dst;
-};
-int upload_pieces(rtb_scene *sc, const std::vector<Piece> &pieces) {
-    size_t total = 0;
-    for (const Piece &p : pieces) total += (p.bytes + 255) / 256 * 256;
-    for (const Piece &p : pieces) *p.dst = nullptr;
-    if (total == 0) return RTB_OK;
-    void *base = nullptr;
-    RTB_CUDA(cudaMalloc(&base, total));
-    sc->allocs.push_back(base);
-    sc->hot_base = base;
-    sc->hot_bytes = total;
-    size_t off = 0;
-    for (const Piece &p : pieces) {
-        if (p.bytes == 0) continue;
-        RTB_CUDA(cudaMemcpy((char *) base + off, p.src, p.bytes, cudaMemcpyHostToDevice));
-        *p.dst = (char *) base + off;
-        sc->upload_bytes += p.bytes;
-        off += (p.bytes + 255) / 256 * 256;
+// The whole scene goes into ONE device allocation (256-byte aligned pieces): one cudaMalloc / cudaFree instead of ~80,
+// and the per-hit records, added first, form a prefix that a single L2 access-policy window can cover.  The copy is
+// staged through two pinned buffers per host thread (allocated once, reused by every later scene): a few host threads
+// fill one buffer while the DMA engine drains the other.  A pageable cudaMemcpy stages through the driver on one
+// thread: 66 ms for the 335 MB Sponza stand-in, measured (tools/e2e_probe.py); this path is part of bench.py's e2e step.
+class Uploader {
+  public:
+    // returns the piece's index; *dst receives base + offset in run()
+    void add(const void *src, size_t bytes, const void **dst) {
+        pieces_.push_back({src, bytes, total_, dst});
+        total_ += (bytes + 255) / 256 * 256;
     }
-    return RTB_OK;
-}
+    size_t total() const { return total_; }
+    // allocates; pointers are valid (but their contents not yet copied) after this
+    int alloc(rtb_scene *sc) {
+        for (auto &p : pieces_) *p.dst = nullptr;
+        if (total_ == 0) return RTB_OK;
+        RTB_CUDA(cudaMalloc(&base_, total_));
+        sc->allocs.push_back(base_);
+        for (auto &p : pieces_) if (p.bytes) *p.dst = (char *) base_ + p.off;
+        return RTB_OK;
+    }
+    void *base() const { return base_; }
+    int run(rtb_scene *sc) {
+        if (total_ == 0) return RTB_OK;
+        constexpr size_t kBuf = (size_t) 32 << 20;
+        struct Stage {
+            void *buf[2] = {nullptr, nullptr};
+            cudaEvent_t ev[2] = {nullptr, nullptr};
+            cudaStream_t st = nullptr;
+            bool ok = false;
+        };
+        static thread_local Stage stage;   // (lives as long as the thread: pinned memory is expensive to allocate)
+        if (!stage.ok) {
+            bool ok = cudaHostAlloc(&stage.buf[0], kBuf, cudaHostAllocPortable) == cudaSuccess &&
+                      cudaHostAlloc(&stage.buf[1], kBuf, cudaHostAllocPortable) == cudaSuccess;
+            if (!ok) {   // no pinned memory to be had: plain copies
+                cudaGetLastError();
+                for (auto &p : pieces_) if (p.bytes) RTB_CUDA(cudaMemcpy((char *) base_ + p.off, p.src, p.bytes, cudaMemcpyHostToDevice));
+                for (auto &p : pieces_) sc->upload_bytes += p.bytes;
+                return RTB_OK;
+            }
+            stage.ok = true;
+        }
+        // streams and events belong to a device: made per call (cheap)
+        RTB_CUDA(cudaStreamCreateWithFlags(&stage.st, cudaStreamNonBlocking));
+        for (auto &e : stage.ev) RTB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        int k = 0;
+        bool used[2] = {false, false};
+        cudaError_t err = cudaSuccess;
+        for (auto &p : pieces_) {
+            for (size_t done = 0; done < p.bytes && err == cudaSuccess; done += kBuf) {
+                const size_t m = std::min(kBuf, p.bytes - done);
+                if (used[k]) err = cudaEventSynchronize(stage.ev[k]);
+                parallel_copy(stage.buf[k], (const char *) p.src + done, m);
+                if (err == cudaSuccess) err = cudaMemcpyAsync((char *) base_ + p.off + done, stage.buf[k], m, cudaMemcpyHostToDevice, stage.st);
+                if (err == cudaSuccess) err = cudaEventRecord(stage.ev[k], stage.st);
+                used[k] = true;
+                k ^= 1;
+            }
+            sc->upload_bytes += p.bytes;
+        }
+        if (err == cudaSuccess) err = cudaStreamSynchronize(stage.st);
+        for (auto &e : stage.ev) cudaEventDestroy(e);
+        cudaStreamDestroy(stage.st);
+        RTB_CUDA(err);
+        return RTB_OK;
+    }
+
+  private:
+    static void parallel_copy(void *dst, const void *src, size_t bytes) {
+        constexpr size_t kMinPerThread = (size_t) 2 << 20;
+        const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+        const size_t nt = std::min<size_t>(std::min<size_t>(4, hw), std::max<size_t>(1, bytes / kMinPerThread));
+        if (nt <= 1) { std::memcpy(dst, src, bytes); return; }
+        std::vector<std::thread> th;
+        const size_t per = (bytes / nt + 63) / 64 * 64;
+        for (size_t t = 0; t < nt; ++t) {
+            const size_t b = t * per, e = std::min(bytes, b + per);
+            if (b >= e) break;
+            th.emplace_back([=] { std::memcpy((char *) dst + b, (const char *) src + b, e - b); });
+        }
+        for (auto &t : th) t.join();
+    }
+    struct P {
+        const void *src;
+        size_t bytes, off;
+        const void **dst;
+    };
+    std::vector<P> pieces_;
+    size_t total_ = 0;
+    void *base_ = nullptr;
+};
 
 // The per-hit records are read at random, once per ray or per shaded hit, while hundreds of MB of path state and texture
 // taps stream through the L2 every iteration and evict them (profiles/r01k_k_wf_shade_summary.txt: 20 % L2 hit rate in
@@ -197,40 +242,43 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
         return fail(RTB_ERR_INVALID);
     }
     int rc;
-    {
-        auto piece = [](const auto &v, auto **dst) {
-            return Piece{v.data(), v.size() * sizeof(v[0]), (const void **) dst};
-        };
-        const std::vector<Piece> pieces = {piece(L.bvh.nodes, &sc->d.bvh.nodes), piece(L.bvh.tris, &sc->d.bvh.tris), piece(L.bvh.big, &sc->d.bvh.big_leaves),
-                                           piece(L.shade, &sc->d.tri_shade), piece(L.tan, &sc->d.tri_tan), piece(L.material, &sc->d.mesh_material),
-                                           piece(L.normal_transform, &sc->d.mesh_normal_transform)};
-        if ((rc = upload_pieces(sc, pieces)) != RTB_OK) return fail(rc);
-        fill_bvh_scalars(L.bvh, sc->d.bvh, desc->n_tris);
-        setup_l2_window(sc);
-    }
-    sc->traversal_bytes = L.bvh.nodes.size() * sizeof(DNode) + L.bvh.tris.size() * sizeof(float4);
-    if (desc->n_lights > 0) {
-        if ((rc = upload_bvh(sc, L.light_bvh, sc->d.light_bvh, desc->n_lights)) != RTB_OK) return fail(rc);
-        if ((rc = upload(sc, L.light_bvh.inv_area, &sc->d.light_inv_area)) != RTB_OK) return fail(rc);
-    }
-    sc->d.n_meshes = L.n_meshes;
-    {
-        std::vector<DTexture> tex(desc->n_textures);
-        for (uint32_t i = 0; i < desc->n_textures; ++i) {
-            const rtb_texture_desc &t = desc->textures[i];
-            const size_t bytes = (size_t) t.width * t.height * 4;
-            void *p = nullptr;
-            RTB_CUDA(cudaMalloc(&p, bytes));
-            sc->allocs.push_back(p);
-            RTB_CUDA(cudaMemcpy(p, t.rgba, bytes, cudaMemcpyHostToDevice));
-            sc->upload_bytes += bytes;
-            tex[i] = {(const uchar4 *) p, t.width, t.height};
-        }
-        if ((rc = upload(sc, tex, &sc->d.textures)) != RTB_OK) return fail(rc);
-    }
-    fill_scalars(desc, sc->d);
     fill_lut(L.lut);
-    if ((rc = upload(sc, L.lut, &sc->d.lut)) != RTB_OK) return fail(rc);
+    std::vector<DTexture> tex(desc->n_textures);
+    std::vector<const void *> tex_ptr(desc->n_textures, nullptr);
+    Uploader up;
+    auto add = [&up](const auto &v, auto **dst) { up.add(v.data(), v.size() * sizeof(v[0]), (const void **) dst); };
+    // the per-hit records first: they are the L2 window (setup_l2_window)
+    add(L.bvh.nodes, &sc->d.bvh.nodes);
+    add(L.bvh.tris, &sc->d.bvh.tris);
+    add(L.bvh.big, &sc->d.bvh.big_leaves);
+    add(L.shade, &sc->d.tri_shade);
+    add(L.tan, &sc->d.tri_tan);
+    add(L.material, &sc->d.mesh_material);
+    add(L.normal_transform, &sc->d.mesh_normal_transform);
+    const size_t hot_bytes = up.total();
+    if (desc->n_lights > 0) {
+        add(L.light_bvh.nodes, &sc->d.light_bvh.nodes);
+        add(L.light_bvh.tris, &sc->d.light_bvh.tris);
+        add(L.light_bvh.big, &sc->d.light_bvh.big_leaves);
+        add(L.light_bvh.inv_area, &sc->d.light_inv_area);
+    }
+    add(L.lut, &sc->d.lut);
+    add(tex, &sc->d.textures);   // (filled in once the texels' device addresses are known, before the copy runs)
+    for (uint32_t i = 0; i < desc->n_textures; ++i) {
+        const rtb_texture_desc &t = desc->textures[i];
+        up.add(t.rgba, (size_t) t.width * t.height * 4, &tex_ptr[i]);
+    }
+    if ((rc = up.alloc(sc)) != RTB_OK) return fail(rc);
+    for (uint32_t i = 0; i < desc->n_textures; ++i) tex[i] = {(const uchar4 *) tex_ptr[i], desc->textures[i].width, desc->textures[i].height};
+    if ((rc = up.run(sc)) != RTB_OK) return fail(rc);
+    sc->hot_base = hot_bytes ? up.base() : nullptr;
+    sc->hot_bytes = hot_bytes;
+    fill_bvh_scalars(L.bvh, sc->d.bvh, desc->n_tris);
+    if (desc->n_lights > 0) fill_bvh_scalars(L.light_bvh, sc->d.light_bvh, desc->n_lights);
+    setup_l2_window(sc);
+    sc->traversal_bytes = L.bvh.nodes.size() * sizeof(DNode) + L.bvh.tris.size() * sizeof(float4);
+    sc->d.n_meshes = L.n_meshes;
+    fill_scalars(desc, sc->d);
 
     RTB_CUDA(cudaMalloc((void **) &sc->queue_heads, kQueueHeads * sizeof(unsigned)));
     for (auto &s : sc->streams) RTB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
