@@ -311,7 +311,15 @@ def roofline(r):
         traffic = t.get("dram_bytes_per_launch") if t else None
     n_samples = r["n_local"] * r["W"] * r["S"]
     rays = max(1.0, st["closest_hit_rays"] * scale)
-    return {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+    # the L2 figures the L2-resident scenes are really up against: measured here, on this GPU
+    l2 = None
+    try:
+        stream_gbs, gather_gbs = rtb.measure_l2(sc.device, 32 << 20)
+        l2 = {"stream_gbs": stream_gbs, "gather64_gbs": gather_gbs, "frac_of_stream": achieved / stream_gbs, "frac_of_gather64": achieved / gather_gbs,
+              "how": "rtb_measure_l2: 32 MB buffer, coalesced 16-byte loads / 64-byte records at random indices (2 x LDG.256)"}
+    except Exception as e:   # a measurement aid: never fails the bench
+        l2 = {"error": str(e)}
+    return {"bound": "hbm", "l2": l2, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
             "kernel": kernel, "kernel_launches": int(n_launch), "kernel_ms_total": kernel_ms, "kernel_ms_avg": kernel_ms / max(1, n_launch),
             "kernel_share_of_step": kernel_ms / max(1e-9, kernel_ms + other_ms), "other_kernels_ms_total": other_ms,
             "algorithmic_bytes_per_launch": bytes_all / max(1, n_launch), "peak_source": src,

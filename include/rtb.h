@@ -182,6 +182,11 @@ int rtb_closest_hit_device(rtb_scene *scene, const float *d_rays6, size_t n, int
                            int32_t *d_id, float *d_t, float *d_u, float *d_v, uint8_t *d_inside,
                            unsigned long long *d_counters, void *stream);
 
+/* Measurement aid (no reference counterpart): L2 bandwidth of `device` on a `bytes`-sized buffer (choose one that fits the
+ * L2) -- coalesced streaming reads, and 64-byte records gathered at random indices (an incoherent ray's node / triangle
+ * fetch without the arithmetic).  bench.py reports the traversal's algorithmic bytes against both.                    */
+int rtb_measure_l2(int device, size_t bytes, double *stream_gbs, double *gather64_gbs);
+
 /* Replaces ManyLightsDistribution::pdf (src/utils/random.cpp:179-188) for a batch (test/diagnostic entry). */
 int rtb_light_pdf(rtb_scene *scene, const float *rays6, size_t n, float *pdf);
 

@@ -25,7 +25,7 @@ ABI_SYMBOLS = [
     "rtb_host_scene_load_gltf", "rtb_host_scene_from_triangles", "rtb_host_scene_desc", "rtb_host_scene_bvh_stats",
     "rtb_host_scene_build_seconds", "rtb_host_scene_destroy",
     "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_device", "rtb_scene_traversal_bytes", "rtb_scene_upload_bytes", "rtb_scene_launches", "rtb_scene_stage_ms",
-    "rtb_closest_hit", "rtb_closest_hit_device", "rtb_light_pdf",
+    "rtb_closest_hit", "rtb_closest_hit_device", "rtb_light_pdf", "rtb_measure_l2",
     "rtb_render", "rtb_render_device", "rtb_resolve_device", "rtb_render_local_rows", "rtb_render_global_row",
     "rtb_write_ppm",
 ]
@@ -104,6 +104,7 @@ def lib():
         L.rtb_closest_hit.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int] + [C.c_void_p] * 5 + [C.POINTER(Stats)]
         L.rtb_closest_hit_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int] + [C.c_void_p] * 7
         L.rtb_light_pdf.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.rtb_measure_l2.argtypes = [C.c_int, C.c_size_t, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.rtb_render.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.POINTER(Stats)]
         L.rtb_render_device.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.rtb_resolve_device.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p]
@@ -308,6 +309,13 @@ class Scene:
     def render_device(self, params, d_accum=None, d_rgb8=None, d_counters=None, stream=0):
         """DEVICE output pointers (e.g. torch tensors), asynchronous on `stream` (a cudaStream_t handle)."""
         _check(lib().rtb_render_device(self.h, C.byref(params), _ptr(d_accum), _ptr(d_rgb8), _ptr(d_counters), C.c_void_p(stream)))
+
+
+def measure_l2(device=0, nbytes=32 << 20):
+    """(streaming GB/s, random 64-byte gather GB/s) of the device's L2 on an nbytes buffer"""
+    a, b = C.c_double(0.0), C.c_double(0.0)
+    _check(lib().rtb_measure_l2(device, nbytes, C.byref(a), C.byref(b)))
+    return a.value, b.value
 
 
 def resolve_device(d_accum, n_pixels, samples, d_rgb8, stream=0):

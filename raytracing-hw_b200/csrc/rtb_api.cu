@@ -287,6 +287,13 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
     return RTB_OK;
 }
 
+int rtb_measure_l2(int device, size_t bytes, double *stream_gbs, double *gather64_gbs) {
+    if (rtb_device_count() <= 0) { rtb::set_error("no CUDA device available (this library has no CPU fallback)"); return RTB_ERR_NO_DEVICE; }
+    RTB_CUDA(cudaSetDevice(device));
+    if (rtb::measure_l2(bytes, stream_gbs, gather64_gbs) != 0) { rtb::set_error("rtb_measure_l2: CUDA error"); return RTB_ERR_CUDA; }
+    return RTB_OK;
+}
+
 void rtb_scene_destroy(rtb_scene *scene) { delete scene; }
 int rtb_scene_device(const rtb_scene *scene) { return scene ? scene->device : -1; }
 size_t rtb_scene_traversal_bytes(const rtb_scene *scene) { return scene ? scene->traversal_bytes : 0; }

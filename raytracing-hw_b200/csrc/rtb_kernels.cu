@@ -186,6 +186,66 @@ __global__ void __launch_bounds__(128) k_light_pdf(const __grid_constant__ DScen
     pdf[i] = prob;
 }
 
+// ---- L2 bandwidth probes: the denominators the L2-resident scenes' traversal is compared with (SURVEY.md section 8d asks
+// for a measured L2 figure).  `stream`: every thread walks the buffer with coalesced 16-byte loads, `reps` passes over
+// a buffer that fits the L2.  `gather64`: every thread reads 64-byte records at pseudo-random indices with two 256-bit
+// loads -- the access pattern of an incoherent ray's node / triangle fetch, without any arithmetic behind it.
+__global__ void __launch_bounds__(256) k_l2_stream(const float4 *__restrict__ p, size_t n4, int reps, float *__restrict__ out) {
+    float acc = 0.f;
+    const size_t stride = (size_t) gridDim.x * blockDim.x;
+    for (int r = 0; r < reps; ++r)
+        for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+            const float4 v = __ldcg(p + i);   // (past the L1: one SM's share of the buffer would fit it)
+            acc += v.x + v.y + v.z + v.w;
+        }
+    if (acc == 123.456f) out[0] = acc;   // (keeps the loads alive)
+}
+__global__ void __launch_bounds__(256) k_l2_gather64(const float4 *__restrict__ p, unsigned n_rec, int iters, float *__restrict__ out) {
+    float acc = 0.f;
+    unsigned x = (blockIdx.x * blockDim.x + threadIdx.x) * 2654435761u + 12345u;
+    for (int it = 0; it < iters; ++it) {
+        x = x * 1664525u + 1013904223u;
+        const float4 *q = p + (size_t) ((x >> 8) % n_rec) * 4;
+        float4 a, b, c;
+        int4 d;
+        ldg256(q, a, b);
+        ldg256(q + 2, c, d);
+        acc += a.x + b.y + c.z + (float) d.w;
+    }
+    if (acc == 123.456f) out[0] = acc;
+}
+int measure_l2(size_t bytes, double *stream_gbs, double *gather64_gbs) {
+    bytes = std::max<size_t>(bytes / 64 * 64, 1 << 20);
+    float4 *buf = nullptr;
+    float *out = nullptr;
+    if (cudaMalloc(&buf, bytes) != cudaSuccess || cudaMalloc(&out, 4) != cudaSuccess) { cudaGetLastError(); if (buf) cudaFree(buf); return 1; }
+    cudaMemset(buf, 0, bytes);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int grid = persistent_grid(256, 8);
+    const int reps = 200, iters = 4000;
+    float ms = 0.f;
+    k_l2_stream<<<grid, 256>>>(buf, bytes / 16, 2, out);   // warm the L2
+    cudaEventRecord(e0);
+    k_l2_stream<<<grid, 256>>>(buf, bytes / 16, reps, out);
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    cudaEventElapsedTime(&ms, e0, e1);
+    if (stream_gbs) *stream_gbs = (double) bytes * reps / (ms * 1e-3) * 1e-9;
+    cudaEventRecord(e0);
+    k_l2_gather64<<<grid, 256>>>(buf, (unsigned) (bytes / 64), iters, out);
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    cudaEventElapsedTime(&ms, e0, e1);
+    if (gather64_gbs) *gather64_gbs = (double) grid * 256 * iters * 64.0 / (ms * 1e-3) * 1e-9;
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(buf);
+    cudaFree(out);
+    return cudaGetLastError() == cudaSuccess ? 0 : 1;
+}
+
 void launch_light_pdf(const DScene &sc, const float *d_rays6, size_t n, float *d_pdf, cudaStream_t stream) {
     if (n == 0) return;
     const unsigned block = 128;

@@ -13,6 +13,7 @@ int trace_mode();
 constexpr int kDefaultTraceBlocks = 9;    // sweeps: profiles/r01d_closest_hit_blocks_sweep.jsonl (first form), profiles/r01i_mode3_sweep.txt (form 3)
 int persistent_blocks_per_sm();   // CTAs per SM of the persistent queue kernels (RTB_TRACE_BLOCKS overrides)
 
+int measure_l2(size_t bytes, double *stream_gbs, double *gather64_gbs);   // rtb_kernels.cu: L2 bandwidth probes
 void launch_light_pdf(const DScene &sc, const float *d_rays6, size_t n, float *d_pdf, cudaStream_t stream);
 
 struct RenderLaunch {
