@@ -192,3 +192,36 @@ def test_libm_known_answers():
         subprocess.run(["make", "-C", os.path.dirname(exe), "libm_check"], check=True, stdout=subprocess.DEVNULL)
     r = subprocess.run([exe, "1009"], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout
+
+
+def _big_leaf_scene():
+    """40 + 9 coincident triangles (their centroids cannot be split: leaves of 40 and 9 triangles, and every ray that hits
+    them produces exact ties, which the first triangle in the reference's order must win) among 300 random ones"""
+    rs = np.random.RandomState(7)
+    a = np.array([[0.2, 0.2, 0.5, 0.6, 0.0, 0.0, 0.0, 0.6, 0.0]], np.float32)
+    b = np.array([[0.1, 0.5, 0.3, 0.5, 0.1, 0.1, 0.0, 0.4, 0.2]], np.float32)
+    soup = rs.rand(300, 9).astype(np.float32)
+    soup[:, 3:] = (soup[:, 3:] - 0.5) * 0.3
+    tri = np.concatenate([np.repeat(a, 40, axis=0), soup[:150], np.repeat(b, 9, axis=0), soup[150:]])
+    return rtb.HostScene.from_triangles(tri)
+
+
+def test_big_leaves_and_exact_ties():
+    hs = _big_leaf_scene()
+    _, links = hs.nodes()
+    assert links[:, 4].max() == 40 and np.count_nonzero(links[:, 4] > 7) >= 2
+    rs = np.random.RandomState(8)
+    rays = np.empty((20000, 6), np.float32)
+    rays[:, 0:3] = rs.rand(20000, 3) * 1.4 - 0.2
+    rays[:, 3:6] = rs.rand(20000, 3) * 2 - 1
+    rays[:5000, 0:2] = rs.rand(5000, 2) * 0.5 + 0.15      # aimed at the coincident stack
+    rays[:5000, 2] = -1
+    rays[:5000, 3:6] = [0, 0, 1]
+    want = _util.twin_bvh(hs).closest_hit(rays, counters=True)
+    assert np.count_nonzero(want["id"][:5000] >= 0) > 1000
+    for form in (0, 3, 105):
+        h = _util.devsim_closest_hit_lane(hs, rays, form)
+        for k in ("id", "t", "u", "v"):
+            assert np.array_equal(h[k], want[k]), (form, k)
+    ordered = _util.devsim_closest_hit(hs, rays, rtb.CULL_REFERENCE)
+    assert (ordered["box_tests"], ordered["tri_tests"]) == (want["box_tests"], want["tri_tests"])

@@ -168,3 +168,22 @@ def test_decision_boundary_rays(name, host_scene):
     ref = rtb.Scene(hs, 0).closest_hit(rays, cull=rtb.CULL_REFERENCE)
     for k in ("id", "t", "u", "v", "inside"):
         assert np.array_equal(ref[k], want[k]), k
+
+
+def test_big_leaves_and_exact_ties():
+    """leaves of more than 7 triangles (coincident triangles the builder cannot split) and the exact ties they produce"""
+    import test_devsim
+    hs = test_devsim._big_leaf_scene()
+    rs = np.random.RandomState(8)
+    rays = np.empty((200000, 6), np.float32)
+    rays[:, 0:3] = rs.rand(200000, 3) * 1.4 - 0.2
+    rays[:, 3:6] = rs.rand(200000, 3) * 2 - 1
+    rays[:50000, 0:2] = rs.rand(50000, 2) * 0.5 + 0.15
+    rays[:50000, 2] = -1
+    rays[:50000, 3:6] = [0, 0, 1]
+    want = _util.twin_bvh(hs).closest_hit(rays)
+    sc = rtb.Scene(hs, 0)
+    for cull in (rtb.CULL_REFERENCE, rtb.CULL_GLOBAL):
+        got = sc.closest_hit(rays, cull=cull)
+        for k in ("id", "t", "u", "v", "inside"):
+            assert np.array_equal(got[k], want[k]), (cull, k)
