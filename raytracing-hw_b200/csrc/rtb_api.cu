@@ -44,9 +44,6 @@ struct rtb_scene {
     void *wf_state = nullptr;
     size_t wf_bytes = 0;
     unsigned long long launches = 0;   // kernels launched by rtb_render_device calls on this scene
-    void *hot_base = nullptr;                // one allocation: nodes, triangles, shading records, tangents, materials
-    size_t hot_bytes = 0;                    //   (the per-hit random-access set: given an L2 persistence window)
-    cudaAccessPolicyWindow l2_window = {};   // num_bytes == 0: no window (RTB_L2_PERSIST=0, unsupported, or nothing to pin)
     rtb::WfStreams wf_streams;               // slot-group streams of the wavefront integrator
     bool wf_streams_ok = false;
     std::vector<cudaEvent_t> stage_events;   // RTB_RENDER_STAGE_TIMES: events of the last such frame
@@ -74,8 +71,8 @@ namespace {
 
 using namespace rtb;
 
-// The whole scene goes into ONE device allocation (256-byte aligned pieces): one cudaMalloc / cudaFree instead of ~80,
-// and the per-hit records, added first, form a prefix that a single L2 access-policy window can cover.  The copy is
+// The whole scene goes into ONE device allocation (256-byte aligned pieces): one cudaMalloc / cudaFree instead of ~80.
+// The copy is
 // staged through two pinned buffers per host thread (allocated once, reused by every later scene): a few host threads
 // fill one buffer while the DMA engine drains the other.  A pageable cudaMemcpy stages through the driver on one
 // thread: 66 ms for the 335 MB Sponza stand-in, measured (tools/e2e_probe.py); this path is part of bench.py's e2e step.
@@ -86,7 +83,6 @@ class Uploader {
         pieces_.push_back({src, bytes, total_, dst});
         total_ += (bytes + 255) / 256 * 256;
     }
-    size_t total() const { return total_; }
     // allocates; pointers are valid (but their contents not yet copied) after this
     int alloc(rtb_scene *sc) {
         for (auto &p : pieces_) *p.dst = nullptr;
@@ -96,7 +92,6 @@ class Uploader {
         for (auto &p : pieces_) if (p.bytes) *p.dst = (char *) base_ + p.off;
         return RTB_OK;
     }
-    void *base() const { return base_; }
     int run(rtb_scene *sc) {
         if (total_ == 0) return RTB_OK;
         constexpr size_t kBuf = (size_t) 32 << 20;
@@ -168,37 +163,6 @@ class Uploader {
     void *base_ = nullptr;
 };
 
-// The per-hit records are read at random, once per ray or per shaded hit, while hundreds of MB of path state and texture
-// taps stream through the L2 every iteration and evict them (profiles/r01k_k_wf_shade_summary.txt: 20 % L2 hit rate in
-// the shade step).  They get a persisting access-policy window, sized to what the device lets us set aside.  Measured
-// (profiles/r01k_l2_window_ab.txt): shade step 530 -> 517 us, L2 hit rate 20 -> 25 %, DRAM reads 1.23 -> 1.17 GB per
-// launch, frame +0.2 .. +0.6 %: small, because most of the step's DRAM traffic is texture taps, which no window can hold.
-void setup_l2_window(rtb_scene *sc) {
-    if (const char *e = std::getenv("RTB_L2_PERSIST")) if (std::atoi(e) == 0) return;
-    if (!sc->hot_base || sc->hot_bytes == 0) return;
-    int max_persist = 0, max_window = 0;
-    if (cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, sc->device) != cudaSuccess ||
-        cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, sc->device) != cudaSuccess || max_persist <= 0 || max_window <= 0) {
-        cudaGetLastError();
-        return;
-    }
-    const size_t persist = std::min<size_t>((size_t) max_persist, sc->hot_bytes);
-    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, persist) != cudaSuccess) { cudaGetLastError(); return; }
-    const size_t window = std::min<size_t>((size_t) max_window, sc->hot_bytes);
-    sc->l2_window.base_ptr = sc->hot_base;
-    sc->l2_window.num_bytes = window;
-    sc->l2_window.hitRatio = (float) std::min(1.0, (double) persist / (double) window);
-    sc->l2_window.hitProp = cudaAccessPropertyPersisting;
-    sc->l2_window.missProp = cudaAccessPropertyStreaming;
-}
-void apply_l2_window(const rtb_scene *sc, cudaStream_t stream) {
-    if (sc->l2_window.num_bytes == 0) return;
-    cudaStreamAttrValue v;
-    std::memset(&v, 0, sizeof v);
-    v.accessPolicyWindow = sc->l2_window;
-    if (cudaStreamSetAttribute(stream, cudaStreamAttributeAccessPolicyWindow, &v) != cudaSuccess) cudaGetLastError();
-}
-
 int ensure_stage(rtb_scene *sc, size_t bytes) {
     if (sc->stage_bytes >= bytes) return RTB_OK;
     if (sc->stage) cudaFree(sc->stage);
@@ -247,7 +211,6 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
     std::vector<const void *> tex_ptr(desc->n_textures, nullptr);
     Uploader up;
     auto add = [&up](const auto &v, auto **dst) { up.add(v.data(), v.size() * sizeof(v[0]), (const void **) dst); };
-    // the per-hit records first: they are the L2 window (setup_l2_window)
     add(L.bvh.nodes, &sc->d.bvh.nodes);
     add(L.bvh.tris, &sc->d.bvh.tris);
     add(L.bvh.big, &sc->d.bvh.big_leaves);
@@ -255,7 +218,6 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
     add(L.tan, &sc->d.tri_tan);
     add(L.material, &sc->d.mesh_material);
     add(L.normal_transform, &sc->d.mesh_normal_transform);
-    const size_t hot_bytes = up.total();
     if (desc->n_lights > 0) {
         add(L.light_bvh.nodes, &sc->d.light_bvh.nodes);
         add(L.light_bvh.tris, &sc->d.light_bvh.tris);
@@ -271,11 +233,8 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
     if ((rc = up.alloc(sc)) != RTB_OK) return fail(rc);
     for (uint32_t i = 0; i < desc->n_textures; ++i) tex[i] = {(const uchar4 *) tex_ptr[i], desc->textures[i].width, desc->textures[i].height};
     if ((rc = up.run(sc)) != RTB_OK) return fail(rc);
-    sc->hot_base = hot_bytes ? up.base() : nullptr;
-    sc->hot_bytes = hot_bytes;
     fill_bvh_scalars(L.bvh, sc->d.bvh, desc->n_tris);
     if (desc->n_lights > 0) fill_bvh_scalars(L.light_bvh, sc->d.light_bvh, desc->n_lights);
-    setup_l2_window(sc);
     sc->traversal_bytes = L.bvh.nodes.size() * sizeof(DNode) + L.bvh.tris.size() * sizeof(float4);
     sc->d.n_meshes = L.n_meshes;
     fill_scalars(desc, sc->d);
@@ -451,9 +410,7 @@ int rtb_render_device(rtb_scene *scene, const rtb_render_params *p, float *d_acc
             for (auto &e : scene->wf_streams.join) RTB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
             RTB_CUDA(cudaEventCreateWithFlags(&scene->wf_streams.fork, cudaEventDisableTiming));
             scene->wf_streams_ok = true;
-            for (auto &s : scene->wf_streams.stream) apply_l2_window(scene, s);
         }
-        apply_l2_window(scene, (cudaStream_t) stream);
         rtb::launch_render_wavefront(scene->d, L, scene->wf_state, (cudaStream_t) stream, &scene->launches,
                                      timed ? &scene->stage_events : nullptr, &scene->wf_streams);
         scene->stage_events_valid = timed;

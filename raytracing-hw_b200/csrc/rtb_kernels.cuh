@@ -10,7 +10,7 @@ void launch_closest_hit(const DScene &sc, const float *d_rays6, size_t n, int cu
 int persistent_grid(int threads_per_block, int blocks_per_sm);
 constexpr int kDefaultTraceMode = 4;       // rtb_trace.cuh: 3 / 4 / 5 = one / two / three steps per refill vote (RTB_TRACE_MODE)
 int trace_mode();
-constexpr int kDefaultTraceBlocks = 9;    // sweeps: profiles/r01d_closest_hit_blocks_sweep.jsonl (first form), profiles/r01i_mode3_sweep.txt (form 3)
+constexpr int kDefaultTraceBlocks = 10;   // sweeps: profiles/r01d_closest_hit_blocks_sweep.jsonl (first form), r01i_mode3_sweep.txt, r01l_leaf_link_sweep.txt (form 3)
 int persistent_blocks_per_sm();   // CTAs per SM of the persistent queue kernels (RTB_TRACE_BLOCKS overrides)
 
 int measure_l2(size_t bytes, double *stream_gbs, double *gather64_gbs);   // rtb_kernels.cu: L2 bandwidth probes

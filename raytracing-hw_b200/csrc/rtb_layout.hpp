@@ -26,8 +26,11 @@ struct HostBvhOut {
 
 inline int make_leaf_link(HostBvhOut &o, int first, int count) {
     if (count >= 1 && count <= 7) return kLeafFlag | (count << 28) | first;
-    o.big.push_back(make_int2(first, count));
-    return kLeafFlag | (int) (o.big.size() - 1);
+    // a leaf of more than 7 triangles: a run of table entries {first + 7k, count - 7k}.  The link names the first one
+    // (the whole leaf: what decode_leaf reads); the queue kernels take 7 triangles at a time and step along the run
+    const int index = (int) o.big.size();
+    for (int k = 0; 7 * k < count; ++k) o.big.push_back(make_int2(first + 7 * k, count - 7 * k));
+    return kLeafFlag | index;
 }
 
 // reference-order nodes (aabb6, links5) -> device layout.  Internal nodes are numbered in depth-first (left first)

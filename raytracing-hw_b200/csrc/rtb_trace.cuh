@@ -36,7 +36,8 @@ struct TracePolicy {
 constexpr int kPopLink = (int) 0x8FFFFFFEu;    // "a pop is pending": big-leaf index 2^28-2, never allocated
 
 // One lane's traversal state and its steps.  RTB_HD so that tests/devsim can run the same state machine on the host.
-// States (by `link`): >= 0 internal node to visit; a leaf link while its triangles [tri_i, tri_end) are being tested;
+// States (by `link`): >= 0 internal node to visit; a leaf link while its triangles are being tested (first form: the
+// range [tri_i, tri_end); form 3: the link itself counts down, see pre3);
 // kPopLink: the entries looked at by the last pop were all culled, pop again; kDoneLink: finished / no ray.
 //
 // The pop is branch-free and bounded: it looks at the two topmost deferred siblings at once (two independent
@@ -81,8 +82,8 @@ struct LaneTraversal {
     // form 3 keeps what only the end of a ray needs out of the registers (the 48 / 56-register budgets of 10 / 9 CTAs
     // per SM): the barycentrics of the best hit live in a fixed local-memory slot above the stack (one predicated 64-bit
     // store per improvement, one load per ray) and max|origin| is recomputed when a hit improves.
-    static constexpr int kUvSlot = kMaxStack + 1;
-    static constexpr int kStack3 = kMaxStack + 2;          // entries of the form-3 array
+    static constexpr int kUvSlot = kMaxStack + 2;          // (one entry of headroom above the deepest stack: the next chunk of a big leaf)
+    static constexpr int kStack3 = kMaxStack + 3;          // entries of the form-3 array
     RTB_HD void finish3() {
         const int2 uv = s2[kUvSlot];
         best.u = u2f((uint32_t) uv.x);
@@ -206,7 +207,12 @@ struct LaneTraversal {
     // not yet decoded leaf, or kPopLink); pre3 pops for the lanes that asked for it and decodes fresh leaves.  In the
     // first form these two pieces were inlined at three places each and ran at 3 to 6 active lanes: 20 % of all
     // issued instructions (profiles/r01h_k_wf_trace_lines.txt).  Same visits, same arithmetic, same results.
-    // A leaf link is "fresh" while tri_i == tri_end (node lanes and popping lanes never hold pending triangles).
+    // In form 3 a leaf being worked on IS its link: {1, triangles left (3 bits), next triangle (28 bits)} -- no separate
+    // range registers, nothing to decode; testing a triangle turns (n, i) into (n - 1, i + 1) and the last one into
+    // kPopLink.  (unsigned) link >= kLeafBusy  <=>  a leaf link with at least one triangle left (kPopLink / kDoneLink
+    // and big-leaf table links carry a zero count and lie below).
+    static constexpr unsigned kLeafBusy = 0x90000000u;
+    RTB_HD bool has_tri() const { return (unsigned) link >= kLeafBusy; }
     RTB_HD void pre3(const DBvh &b) {
         if (link == kPopLink) {
             const int i1 = sp - 1, i2 = sp >= 2 ? sp - 2 : 0;
@@ -216,16 +222,16 @@ struct LaneTraversal {
             sp = k1 ? i1 : i2;
             if (link == kDoneLink) sp = 1;
         }
-        const bool fresh = link < 0 && tri_i == tri_end;
-        int count = (link >> 28) & 7;
-        int first = link & 0x0FFFFFFF;
-        if (fresh && count == 0 && first < 0x0FFFFFFE) {     // a leaf with more than 7 triangles (rare)
-            const int2 bl = ldg(&b.big_leaves[first]);
-            first = bl.x;
-            count = bl.y;
+        if ((unsigned) link - 0x80000000u < 0x0FFFFFFEu) {   // a leaf of more than 7 triangles (rare): 7 now, the rest deferred
+            const int2 bl = ldg(&b.big_leaves[link & 0x0FFFFFFF]);
+            int take = bl.y;
+            if (take > 7) {
+                s2[sp] = make_int2(link + 1, (int) f2u(-1.f));   // the next entry of the run; never culled: the leaf has been entered
+                ++sp;
+                take = 7;
+            }
+            link = (int) (0x80000000u | ((unsigned) take << 28) | (unsigned) bl.x);
         }
-        tri_i = fresh ? first : tri_i;
-        tri_end = fresh ? first + count : tri_end;
     }
     template <class C>
     RTB_HD void node_compute3(const float4 na, const float4 nb, const float4 nc, const int4 nd, C *cnt) {
@@ -249,12 +255,12 @@ struct LaneTraversal {
         if (COUNT) cnt->tri += 1;
         if (tri_test_flat(r, q0, q1, q2, t, u, v) && t < best.t) {
             best.t = t;
-            best.id = tri_i;
+            best.id = link & 0x0FFFFFFF;
             s2[kUvSlot] = make_int2((int) f2u(u), (int) f2u(v));
             cull = cull_bound(t, ray_omax(r));
         }
-        ++tri_i;
-        if (tri_i == tri_end) link = kPopLink;
+        const int next = link - 0x0FFFFFFF;       // one triangle fewer, the next index
+        link = (unsigned) next >= kLeafBusy ? next : kPopLink;
     }
     template <class C>
     RTB_HD void step3(const DBvh &b, C *cnt) {
@@ -262,8 +268,8 @@ struct LaneTraversal {
         if (link >= 0) {
             const DNode *np = b.nodes + link;
             node_compute3(ldg(&np->a), ldg(&np->b), ldg(&np->c), ldg(&np->d), cnt);
-        } else if (tri_i < tri_end) {
-            const float4 *tp = b.tris + (size_t) tri_i * kTriStride;
+        } else if (has_tri()) {
+            const float4 *tp = b.tris + (size_t) (link & 0x0FFFFFFF) * kTriStride;
             tri_compute3(ldg(tp), ldg(tp + 1), ldg(tp + 2), cnt);
         }
     }
@@ -355,12 +361,12 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
         for (int step = 0; step < MODE - 2; ++step) {
             L.pre3(b);
             const bool doN = L.link >= 0;
-            const bool doL = L.tri_i < L.tri_end;
+            const bool doL = L.has_tri();
             // One 64-byte record per lane -- its node or its triangle -- with two 256-bit loads (LDG.E.256, new on
             // sm_100): half the load instructions and half the LSU wavefronts of the 4 x LDG.128 form, which ncu showed
             // at 81 % of the LSU data-pipe peak (profiles/r01i_k_wf_trace_summary.txt).  Idle lanes (waiting for a
             // refill or for their next pop) read triangle 0: no predicates, no zeroing.
-            const float4 *p = doN ? reinterpret_cast<const float4 *>(b.nodes + L.link) : (b.tris + (size_t) (doL ? L.tri_i : 0) * kTriStride);
+            const float4 *p = doN ? reinterpret_cast<const float4 *>(b.nodes + L.link) : (b.tris + (size_t) (doL ? L.link & 0x0FFFFFFF : 0) * kTriStride);
             float4 a, bb, c;
             int4 d;
             ldg256(p, a, bb);
@@ -377,7 +383,6 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
                     have_ray = false;
                     L.link = kDoneLink;
                     L.sp = 1;
-                    L.tri_i = L.tri_end = 0;
                 } else {
                     budget = 16;
                 }

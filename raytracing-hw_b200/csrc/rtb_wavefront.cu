@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(kCompactBlock) k_wf_scatter(const unsigned *__
 }
 }  // namespace
 
-static unsigned wf_susp_stride(int bvh_depth) { return (unsigned) (LaneTraversal<false>::kSuspHeader + std::max(0, bvh_depth) + 2); }
+static unsigned wf_susp_stride(int bvh_depth) { return (unsigned) (LaneTraversal<false>::kSuspHeader + std::max(0, bvh_depth) + 3); }
 
 size_t wf_state_bytes(unsigned n_slots, int depth_cap, int bvh_depth) {
     const size_t per_slot = 16 + 8 + 16 + 16 + 16 + (size_t) depth_cap * (16 + 16 + 4) + 2 * 4 + (size_t) wf_susp_stride(bvh_depth) * 8;

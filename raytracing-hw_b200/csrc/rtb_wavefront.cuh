@@ -37,7 +37,7 @@ struct WfState {
     float4 *stk_m;           // [depth_cap][n_slots] material.xyz, cosine
     float *stk_a;            // [depth_cap][n_slots] material alpha
     int2 *susp;              // [n_slots][susp_stride] traversal state of a suspended ray (LaneTraversal::save3)
-    unsigned susp_stride;    // kSuspHeader + BVH depth + 2 entries
+    unsigned susp_stride;    // kSuspHeader + BVH depth + 3 entries
 };
 
 RTB_HD bool wf_slot_pixel(const RenderLaunch &p, unsigned slot, int &px, int &lr, int &py) {

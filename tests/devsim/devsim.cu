@@ -106,7 +106,7 @@ int devsim_closest_hit_lane(const rtb_scene_desc *desc, const float *rays6, size
             // form 3, suspended every (schedule_seed - 100) steps: the state goes through save3 / load3 into a FRESH lane
             // (new stack, ray re-made from the ray record), as the queue kernel does across launches
             const int every = (int) (schedule_seed - 100u);
-            int2 rec[LaneTraversal<true>::kSuspHeader + kMaxStack + 2];
+            int2 rec[LaneTraversal<true>::kSuspHeader + kMaxStack + 3];
             int2 stack3[LaneTraversal<true>::kStack3];
             int left = every;
             while (!L.finished()) {
