@@ -63,9 +63,9 @@ __global__ void __launch_bounds__(128, MINB) k_closest_hit_queue(const __grid_co
                                                            uint8_t *__restrict__ inside, unsigned long long *__restrict__ counters,
                                                            const TracePolicy pol) {
     QueueCounters cnt = {0ull, 0ull, 0u};
-    trace_persistent<COUNT, MODE>(
+    trace_persistent<COUNT, MODE, RTB_RING_BATCH>(
         sc.bvh, n, queue_head,
-        [&](unsigned i, LaneTraversal<COUNT> &L, unsigned &tag) {
+        [&](unsigned i, LaneTraversal<COUNT, RTB_RING_BATCH> &L, unsigned &tag) {
             const float2 *rp = reinterpret_cast<const float2 *>(rays6 + (size_t) i * 6);
             const float2 r0 = __ldg(rp), r1 = __ldg(rp + 1), r2 = __ldg(rp + 2);
             make_ray(L.r, r0.x, r0.y, r1.x, r1.y, r2.x, r2.y);
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(128, MINB) k_closest_hit_queue(const __grid_co
                 inside[i] = in;
             }
         },
-        [](unsigned, const LaneTraversal<COUNT> &) {}, 0,   // a batch is one launch: nothing is ever suspended
+        [](unsigned, LaneTraversal<COUNT, RTB_RING_BATCH> &) {}, 0,   // a batch is one launch: nothing is ever suspended
         &cnt, pol);
     if (COUNT) {
         for (int o = 16; o > 0; o >>= 1) {

@@ -16,7 +16,18 @@
 #pragma once
 #include "rtb_traverse.cuh"
 
+// entries of the form-3 stack kept in shared memory per thread (a power of two; 0: none), per kernel: measured in
+// profiles/r01m_stack_ring_experiment.txt -- the ring wins on incoherent batches (soup +6 %) and loses on the frame (-3.5 %)
+#ifndef RTB_RING_BATCH
+#define RTB_RING_BATCH 8
+#endif
+#ifndef RTB_RING_WAVEFRONT
+#define RTB_RING_WAVEFRONT 0
+#endif
+
 namespace rtb {
+
+constexpr int kRingThreads = 128;   // threads per CTA of the kernels that run the form-3 loop
 
 struct TracePolicy;
 TracePolicy trace_policy();   // rtb_kernels.cu
@@ -44,7 +55,7 @@ constexpr int kPopLink = (int) 0x8FFFFFFEu;    // "a pop is pending": big-leaf i
 // local-memory loads) and, if both are culled, leaves the lane in the kPopLink state for the next iteration.  ncu showed
 // the `do {} while (m > cull)` form running at 2 active lanes with a quarter of all stall samples on its dependent
 // loads (profiles/r01e_k_wf_trace_lines.txt).
-template <bool COUNT>
+template <bool COUNT, int RING = 0>
 struct LaneTraversal {
     // the deferred-sibling stack lives in the caller's frame (dynamically indexed => local memory); keeping the arrays
     // out of this struct lets every other member be promoted to registers
@@ -78,12 +89,47 @@ struct LaneTraversal {
         s2 = stack;
         s2[0] = make_int2(kDoneLink, (int) f2u(-1.f));   // the sentinel is never culled
         s2[kUvSlot] = make_int2(0, 0);
+        rn = 0;
     }
     // form 3 keeps what only the end of a ray needs out of the registers (the 48 / 56-register budgets of 10 / 9 CTAs
     // per SM): the barycentrics of the best hit live in a fixed local-memory slot above the stack (one predicated 64-bit
     // store per improvement, one load per ray) and max|origin| is recomputed when a hit improves.
     static constexpr int kUvSlot = kMaxStack + 2;          // (one entry of headroom above the deepest stack: the next chunk of a big leaf)
     static constexpr int kStack3 = kMaxStack + 3;          // entries of the form-3 array
+    // The top kRing entries of the form-3 stack live in a ring (shared memory on the device, [slot][thread]: a 64-bit
+    // access per lane is conflict-free whatever slot each lane is at, 2 wavefronts per warp instruction); the array in
+    // local memory is the backing store: entries [0, sp - rn) are there, [sp - rn, sp) are in the ring, an entry is
+    // written back to its place in the array only when a push finds the ring full.  Local memory interleaves 32-bit
+    // words across the lanes, so a lane's 8-byte entry costs 2 sectors = 2 LSU wavefronts per LANE at divergent
+    // depths: pushes and pops were 36 % of the LSU data-pipe work of the trace kernel, the unit that bounds it at 86 %
+    // of peak (profiles/r01m_k_wf_trace_summary.txt).  kRing == 0: no ring, everything in the array.
+    static constexpr int kRing = RING;
+    static_assert((kRing & (kRing - 1)) == 0, "the ring size is a power of two");
+    int rn;                                                // entries in the ring
+#ifndef __CUDA_ARCH__
+    int2 host_ring[kRing > 0 ? kRing : 1];
+#endif
+    RTB_HD int2 &ring_at(int i) {
+#ifdef __CUDA_ARCH__
+        __shared__ int2 ring[(kRing > 0 ? kRing : 1) * kRingThreads];
+        return ring[(i & (kRing - 1)) * kRingThreads + threadIdx.x];
+#else
+        return host_ring[i & (kRing - 1)];
+#endif
+    }
+    RTB_HD void push3(const int2 e) {
+        if (kRing > 0) {
+            int2 &slot = ring_at(sp);
+            if (rn == kRing) s2[sp - kRing] = slot;       // the oldest entry makes room
+            else ++rn;
+            slot = e;
+        } else {
+            s2[sp] = e;
+        }
+        ++sp;
+    }
+    // entry i of the stack wherever it lives (suspending)
+    RTB_HD int2 entry3(int i) { return (kRing > 0 && i >= sp - rn) ? ring_at(i) : s2[i]; }
     RTB_HD void finish3() {
         const int2 uv = s2[kUvSlot];
         best.u = u2f((uint32_t) uv.x);
@@ -92,13 +138,13 @@ struct LaneTraversal {
     // ---- suspending a ray (form 3): everything a later launch needs to carry on from exactly this state.  The ray
     // itself is re-made from the caller's ray record (make_ray is a pure function of it).  rec: kSuspHeader + sp entries.
     static constexpr int kSuspHeader = 5;
-    RTB_HD void save3(int2 *rec) const {
+    RTB_HD void save3(int2 *rec) {
         rec[0] = make_int2(link, sp);
         rec[1] = make_int2(tri_i, tri_end);
         rec[2] = make_int2((int) f2u(best.t), best.id);
         rec[3] = make_int2((int) f2u(cull), 0);
         rec[4] = s2[kUvSlot];
-        for (int i = 0; i < sp; ++i) rec[kSuspHeader + i] = s2[i];
+        for (int i = 0; i < sp; ++i) rec[kSuspHeader + i] = entry3(i);
     }
     // `r` has been set (as for begin)
     RTB_HD void load3(const int2 *rec) {
@@ -109,6 +155,7 @@ struct LaneTraversal {
         cull = u2f((uint32_t) d.x);
         s2[kUvSlot] = rec[4];
         for (int i = 0; i < sp; ++i) s2[i] = rec[kSuspHeader + i];
+        rn = 0;
         omax = ray_omax(r);
         sgn = (r.d[0] > 0.f ? 1u : 0u) | (r.d[1] > 0.f ? 2u : 0u) | (r.d[2] > 0.f ? 4u : 0u);
     }
@@ -216,18 +263,27 @@ struct LaneTraversal {
     RTB_HD void pre3(const DBvh &b) {
         if (link == kPopLink) {
             const int i1 = sp - 1, i2 = sp >= 2 ? sp - 2 : 0;
-            const int2 e1 = s2[i1], e2 = s2[i2];
+            int2 e1, e2;
+            if (kRing > 0) {
+                e1 = ring_at(i1);
+                e2 = ring_at(i2);
+                if (rn < 1) e1 = s2[i1];
+                if (rn < 2) e2 = s2[i2];
+            } else {
+                e1 = s2[i1];
+                e2 = s2[i2];
+            }
             const bool k1 = !(u2f((uint32_t) e1.y) > cull), k2 = !(u2f((uint32_t) e2.y) > cull);
             link = k1 ? e1.x : (k2 ? e2.x : kPopLink);
             sp = k1 ? i1 : i2;
-            if (link == kDoneLink) sp = 1;
+            if (kRing > 0) { rn -= k1 ? 1 : 2; rn = rn < 0 ? 0 : rn; }
+            if (link == kDoneLink) sp = 1;                 // (the sentinel is entry 0 of the array, never in the ring)
         }
         if ((unsigned) link - 0x80000000u < 0x0FFFFFFEu) {   // a leaf of more than 7 triangles (rare): 7 now, the rest deferred
             const int2 bl = ldg(&b.big_leaves[link & 0x0FFFFFFF]);
             int take = bl.y;
             if (take > 7) {
-                s2[sp] = make_int2(link + 1, (int) f2u(-1.f));   // the next entry of the run; never culled: the leaf has been entered
-                ++sp;
+                push3(make_int2(link + 1, (int) f2u(-1.f)));     // the next entry of the run; never culled: the leaf has been entered
                 take = 7;
             }
             link = (int) (0x80000000u | ((unsigned) take << 28) | (unsigned) bl.x);
@@ -243,10 +299,7 @@ struct LaneTraversal {
         const bool left_first = ((sgn >> nd.z) & 1u) != 0u;   // direction[split_dim] > 0 (bvh.cpp:183)
         const bool both = vl && vr;
         const bool take_left = vl && (left_first || !vr);    // both ? left_first : vl
-        if (both) {
-            s2[sp] = make_int2(take_left ? nd.y : nd.x, (int) f2u(take_left ? mr : ml));
-            ++sp;
-        }
+        if (both) push3(make_int2(take_left ? nd.y : nd.x, (int) f2u(take_left ? mr : ml)));
         link = (vl || vr) ? (take_left ? nd.x : nd.y) : kPopLink;
     }
     template <class C>
@@ -309,13 +362,13 @@ __device__ __forceinline__ void ldg256(const float4 *p, float4 &lo, int4 &hi) {
 // later launch resumes it where it stopped.  Without this a launch lasts as long as its longest ray (hundreds of
 // steps against a mean of ~50), which is what bounds small frames / many GPUs (profiles/r01k_*): the iterations of a
 // pixel are a dependent chain.  The ray's visits, arithmetic and result are unchanged; only when they happen moves.
-template <bool COUNT, int MODE, class Fetch, class Emit, class Suspend>
+template <bool COUNT, int MODE, int RING, class Fetch, class Emit, class Suspend>
 __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsigned *queue_head, Fetch fetch, Emit emit, Suspend suspend,
                                                  const int tail_steps, QueueCounters *cnt, const TracePolicy pol) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    __align__(8) int2 stack[LaneTraversal<COUNT>::kStack3];
-    LaneTraversal<COUNT> L;
+    __align__(8) int2 stack[LaneTraversal<COUNT, RING>::kStack3];
+    LaneTraversal<COUNT, RING> L;
     L.reset3(stack);
     unsigned tag = 0;
     bool have_ray = false, exhausted = false;
@@ -383,6 +436,7 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
                     have_ray = false;
                     L.link = kDoneLink;
                     L.sp = 1;
+                    L.rn = 0;
                 } else {
                     budget = 16;
                 }

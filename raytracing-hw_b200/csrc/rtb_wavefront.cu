@@ -50,9 +50,9 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(const __grid_constant__ 
     if (n == 0 || (blockIdx.x > 0 && blockIdx.x * (128u * rays_per_lane) >= n)) return;
     QueueCounters cnt = {0ull, 0ull, 0u};
     // the tag of a ray is its index in the active list: the entry says which slot it is and whether it was suspended
-    trace_persistent<COUNT, MODE>(
+    trace_persistent<COUNT, MODE, RTB_RING_WAVEFRONT>(
         sc.bvh, n, queue_head,
-        [&](unsigned i, LaneTraversal<COUNT> &L, unsigned &tag) {
+        [&](unsigned i, LaneTraversal<COUNT, RTB_RING_WAVEFRONT> &L, unsigned &tag) {
             const unsigned e = list[i];
             if (e & kSlotDone) return 0;
             tag = i;
@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(const __grid_constant__ 
             w.hit[e & kSlotIndex] = make_float4(h.t, h.u, h.v, u2f((uint32_t) h.id));
             if (e & kSlotSuspended) list[i] = e & ~kSlotSuspended;
         },
-        [&](unsigned i, const LaneTraversal<COUNT> &L) {
+        [&](unsigned i, LaneTraversal<COUNT, RTB_RING_WAVEFRONT> &L) {
             const unsigned e = list[i];
             L.save3(w.susp + (size_t) (e & kSlotIndex) * w.susp_stride);
             if (!(e & kSlotSuspended)) list[i] = e | kSlotSuspended;

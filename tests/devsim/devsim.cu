@@ -48,6 +48,35 @@ bool make_scene(const rtb_scene_desc *desc, SimScene &s, std::string &err) {
 std::string g_err;
 }  // namespace
 
+// Form 3 of the per-lane state machine with a RING-entry ring on top of the stack; every > 0: the state goes through
+// save3 / load3 into a FRESH lane (new stack, new ring, ray re-made from the ray record) every `every` steps, as the
+// queue kernel does across launches.
+template <int RING>
+static Hit lane_form3(const DBvh &bvh, const float *ray6, int every, Counters &c) {
+    using Lane = LaneTraversal<true, RING>;
+    int2 stack2[Lane::kStack3], stack3[Lane::kStack3];
+    int2 rec[Lane::kSuspHeader + kMaxStack + 3];
+    Lane L;
+    L.reset3(stack2);
+    make_ray(L.r, ray6[0], ray6[1], ray6[2], ray6[3], ray6[4], ray6[5]);
+    L.begin(bvh, &c);
+    int left = every;
+    while (!L.finished()) {
+        L.step3(bvh, &c);
+        if (every > 0 && --left <= 0 && !L.finished()) {
+            L.save3(rec);
+            Lane M;
+            M.reset3(L.s2 == stack2 ? stack3 : stack2);
+            make_ray(M.r, ray6[0], ray6[1], ray6[2], ray6[3], ray6[4], ray6[5]);
+            M.load3(rec);
+            L = M;
+            left = every;
+        }
+    }
+    L.finish3();
+    return L.best;
+}
+
 extern "C" {
 
 const char *devsim_last_error() { return g_err.c_str(); }
@@ -84,6 +113,8 @@ int devsim_closest_hit(const rtb_scene_desc *desc, const float *rays6, size_t n,
 }
 
 // The queue kernels' per-lane state machine (rtb_trace.cuh: LaneTraversal, bounded branch-free pops) on the host.
+// schedule_seed selects the form: 0..2 the first form; 3 form 3 (one pop site per step); 4 / 5 form 3 with a 2- / 8-entry
+// ring on top of the stack; 100 + n form 3 suspended every n steps; 10000 + n the same with the 2-entry ring.
 int devsim_closest_hit_lane(const rtb_scene_desc *desc, const float *rays6, size_t n, unsigned schedule_seed, int32_t *id, float *t,
                             float *u, float *v, unsigned long long *counters2) {
     SimScene s;
@@ -91,46 +122,31 @@ int devsim_closest_hit_lane(const rtb_scene_desc *desc, const float *rays6, size
     unsigned long long box = 0, tri = 0;
 #pragma omp parallel for schedule(dynamic, 1024) reduction(+ : box, tri)
     for (size_t i = 0; i < n; ++i) {
-        int stack_link[kMaxStack + 1];
-        float stack_m[kMaxStack + 1];
-        int2 stack2[LaneTraversal<true>::kStack3];
-        LaneTraversal<true> L;
-        L.reset(stack_link, stack_m);
-        if (schedule_seed >= 3u) L.reset3(stack2);
-        make_ray(L.r, rays6[i * 6], rays6[i * 6 + 1], rays6[i * 6 + 2], rays6[i * 6 + 3], rays6[i * 6 + 4], rays6[i * 6 + 5]);
         Counters c = {0, 0};
-        L.begin(s.d.bvh, &c);
-        // schedule_seed selects the form of the state machine: 3 = one pop / decode site per step (MODE 3), else the first form
-        if (schedule_seed == 3u) { while (!L.finished()) L.step3(s.d.bvh, &c); L.finish3(); }
-        else if (schedule_seed >= 100u) {
-            // form 3, suspended every (schedule_seed - 100) steps: the state goes through save3 / load3 into a FRESH lane
-            // (new stack, ray re-made from the ray record), as the queue kernel does across launches
-            const int every = (int) (schedule_seed - 100u);
-            int2 rec[LaneTraversal<true>::kSuspHeader + kMaxStack + 3];
-            int2 stack3[LaneTraversal<true>::kStack3];
-            int left = every;
-            while (!L.finished()) {
-                L.step3(s.d.bvh, &c);
-                if (--left <= 0 && !L.finished()) {
-                    L.save3(rec);
-                    LaneTraversal<true> M;
-                    M.reset3(L.s2 == stack2 ? stack3 : stack2);
-                    make_ray(M.r, rays6[i * 6], rays6[i * 6 + 1], rays6[i * 6 + 2], rays6[i * 6 + 3], rays6[i * 6 + 4], rays6[i * 6 + 5]);
-                    M.load3(rec);
-                    L = M;
-                    left = every;
-                }
-            }
-            L.finish3();
+        Hit best;
+        const float *ray6 = rays6 + i * 6;
+        if (schedule_seed >= 10000u) best = lane_form3<2>(s.d.bvh, ray6, (int) (schedule_seed - 10000u), c);
+        else if (schedule_seed >= 100u) best = lane_form3<0>(s.d.bvh, ray6, (int) (schedule_seed - 100u), c);
+        else if (schedule_seed == 5u) best = lane_form3<8>(s.d.bvh, ray6, 0, c);
+        else if (schedule_seed == 4u) best = lane_form3<2>(s.d.bvh, ray6, 0, c);
+        else if (schedule_seed == 3u) best = lane_form3<0>(s.d.bvh, ray6, 0, c);
+        else {
+            int stack_link[kMaxStack + 1];
+            float stack_m[kMaxStack + 1];
+            LaneTraversal<true> L;
+            L.reset(stack_link, stack_m);
+            make_ray(L.r, ray6[0], ray6[1], ray6[2], ray6[3], ray6[4], ray6[5]);
+            L.begin(s.d.bvh, &c);
+            while (!L.finished()) L.step(s.d.bvh, &c);
+            best = L.best;
         }
-        else while (!L.finished()) L.step(s.d.bvh, &c);
         box += c.box;
         tri += c.tri;
-        const bool ok = L.best.id >= 0;
-        id[i] = ok ? L.best.id : -1;
-        if (t) t[i] = ok ? L.best.t : 0.f;
-        if (u) u[i] = ok ? L.best.u : 0.f;
-        if (v) v[i] = ok ? L.best.v : 0.f;
+        const bool ok = best.id >= 0;
+        id[i] = ok ? best.id : -1;
+        if (t) t[i] = ok ? best.t : 0.f;
+        if (u) u[i] = ok ? best.u : 0.f;
+        if (v) v[i] = ok ? best.v : 0.f;
     }
     if (counters2) { counters2[0] = box; counters2[1] = tri; }
     return 0;

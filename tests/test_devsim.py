@@ -74,6 +74,22 @@ def test_lane_form3_suspend_resume(name, every, host_scene):
 
 
 @pytest.mark.parametrize("name", SCENES)
+@pytest.mark.parametrize("form", [4, 5, 10001, 10007])
+def test_lane_form3_stack_ring(name, form, host_scene):
+    """the top of the form-3 stack in a ring (what the batched queue kernel keeps in shared memory; LaneTraversal::push3 /
+    pre3 / entry3) with the array as backing store: a 2-entry ring overflows and refills all the time, an 8-entry one
+    rarely; alone and combined with suspend / resume.  Same tests, same answers as the plain array."""
+    g = _util.load_golden(name)
+    hs = host_scene(name)
+    rays = np.concatenate([_util.box_rays(g["root_box"], 4096, seed=1000), _util.edge_rays(hs, g["root_box"], 4096, seed=78)])
+    plain = _util.devsim_closest_hit_lane(hs, rays, 3)
+    ring = _util.devsim_closest_hit_lane(hs, rays, form)
+    assert (ring["box_tests"], ring["tri_tests"]) == (plain["box_tests"], plain["tri_tests"])
+    for k in ("id", "t", "u", "v"):
+        assert np.array_equal(ring[k], plain[k]), k
+
+
+@pytest.mark.parametrize("name", SCENES)
 def test_lane_form3_on_decision_boundaries(name, host_scene):
     """rays that sit on the box test's decision boundaries (zero direction components, origins on box planes, rays
     through box corners): form 3 vs the twin (the pinned restatement of the reference's recursion)"""
