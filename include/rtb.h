@@ -93,8 +93,9 @@ typedef struct rtb_render_params {
     int32_t row_begin, row_end;   /* rows [row_begin,row_end) rendered by this call (tile split); 0,height = all     */
     uint32_t pixel0_seed;         /* engine seed of pixel 0 (the reference uses std::random_device there,
                                      src/utils/random.cpp:12-18); 0 is mapped to 1 as minstd_rand::seed does          */
-    int32_t sample_begin;         /* reserved, must be 0: all samples of a pixel share ONE sequential engine stream
-                                     (src/core/scene.cpp:34-35), so a pixel's sample range cannot be cut              */
+    int32_t sample_begin;         /* 0, or -- rtb_render_resume only -- the samples per pixel an earlier call has
+                                     already taken: all samples of a pixel share ONE sequential engine stream
+                                     (src/core/scene.cpp:34-35), so a frame can only be continued, not cut freely      */
     int32_t flags;                /* RTB_RENDER_* bits                                                                */
     /* multi-GPU tile split: rows [row_begin,row_end) are cut into blocks of `interleave_rows` rows (a multiple of 4);
      * this call renders the blocks b with b % interleave_count == interleave_index and writes them COMPACTLY, in block
@@ -201,6 +202,33 @@ int rtb_render(rtb_scene *scene, const rtb_render_params *params, float *accum, 
  * light-query box, light-query tri} or NULL (box / tri are totals over both BVHs and need RTB_RENDER_COUNTERS)    */
 int rtb_render_device(rtb_scene *scene, const rtb_render_params *params, float *d_accum, uint8_t *d_rgb8,
                       unsigned long long *d_counters, void *stream);
+
+/* ---- progressive rendering: checkpoint / resume and the progress line -------------------
+ * The state of a pixel BETWEEN two samples is its engine (minstd_rand value + the cached half of the Marsaglia pair,
+ * src/utils/random.cpp) and its radiance sum (src/core/scene.cpp:42): RTB_PIXEL_STATE_BYTES per pixel, in the order
+ * of the call's local rows.  rtb_render_resume renders samples [params->sample_begin, params->samples) of every pixel:
+ *   state in : read when sample_begin > 0 (what an earlier call with samples == sample_begin wrote);
+ *   state out: the state after params->samples samples (always written);
+ *   accum / rgb8: the sums / the resolved image after params->samples samples (divided by params->samples), i.e.
+ *   exactly what ONE call with these `samples` and sample_begin == 0 returns -- bit for bit
+ *   (tests/test_gpu_render.py::test_resume_is_bit_identical).  A caller can therefore write a preview image after
+ *   every chunk, stop, store `state` in a file and carry on later -- on another GPU if it likes.
+ * Wavefront integrator only (RTB_ERR_INVALID with RTB_RENDER_MEGAKERNEL / RTB_RENDER_REFERENCE_CULL).
+ * rtb_render(scene, p, accum, rgb8, stats) == rtb_render_resume(scene, p, NULL, accum, rgb8, stats).                  */
+#define RTB_PIXEL_STATE_BYTES 32
+size_t rtb_render_state_bytes(const rtb_render_params *params);
+int rtb_render_resume(rtb_scene *scene, const rtb_render_params *params, void *state, float *accum, uint8_t *rgb8,
+                      rtb_stats *stats);
+/* the same with device buffers, stream-ordered (d_pixel_state may be NULL when sample_begin == 0) */
+int rtb_render_resume_device(rtb_scene *scene, const rtb_render_params *params, void *d_pixel_state, float *d_accum,
+                             uint8_t *d_rgb8, unsigned long long *d_counters, void *stream);
+/* Progress line: the reference's USE_CALLBACK build calls ProgressCallback(percent, timer) once per pixel
+ * (src/main.cpp:8-20, src/core/scene.cpp:45-50).  Here fn(percent, user) is called on the rendering thread, with 0 when
+ * the frame starts, with the share of the frame's queue iterations that have completed (<= 99) while it runs, and
+ * with 100 when it is complete; with a callback set a render call returns only when the frame is done.  fn == NULL:
+ * off (default).  The return value is ignored, as the reference ignores it.                                          */
+typedef int (*rtb_progress_fn)(int percent, void *user);
+int rtb_scene_set_progress(rtb_scene *scene, rtb_progress_fn fn, void *user);
 /* resolve only (src/core/scene.cpp:54-63): d_accum (n_pixels x 3 sums) -> d_rgb8 */
 int rtb_resolve_device(const float *d_accum, size_t n_pixels, int samples, uint8_t *d_rgb8, void *stream);
 

@@ -27,6 +27,7 @@ ABI_SYMBOLS = [
     "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_device", "rtb_scene_traversal_bytes", "rtb_scene_upload_bytes", "rtb_scene_launches", "rtb_scene_stage_ms",
     "rtb_closest_hit", "rtb_closest_hit_device", "rtb_light_pdf", "rtb_measure_l2",
     "rtb_render", "rtb_render_device", "rtb_resolve_device", "rtb_render_local_rows", "rtb_render_global_row",
+    "rtb_render_resume", "rtb_render_resume_device", "rtb_render_state_bytes", "rtb_scene_set_progress",
     "rtb_write_ppm",
 ]
 
@@ -62,6 +63,10 @@ class Stats(C.Structure):
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+PROGRESS_FN = C.CFUNCTYPE(C.c_int, C.c_int, C.c_void_p)   # rtb_progress_fn
+PIXEL_STATE_BYTES = 32
 
 
 class RtbError(RuntimeError):
@@ -107,6 +112,11 @@ def lib():
         L.rtb_measure_l2.argtypes = [C.c_int, C.c_size_t, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.rtb_render.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.POINTER(Stats)]
         L.rtb_render_device.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.rtb_render_resume.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(Stats)]
+        L.rtb_render_resume_device.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.rtb_render_state_bytes.argtypes = [C.POINTER(RenderParams)]
+        L.rtb_render_state_bytes.restype = C.c_size_t
+        L.rtb_scene_set_progress.argtypes = [C.c_void_p, PROGRESS_FN, C.c_void_p]
         L.rtb_resolve_device.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p]
         L.rtb_write_ppm.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p]
         _lib = L
@@ -305,6 +315,34 @@ class Scene:
         st = Stats()
         _check(lib().rtb_render(self.h, C.byref(params), _ptr(accum), _ptr(rgb), C.byref(st)))
         return dict(accum=accum, rgb=rgb, stats=st.as_dict())
+
+    def render_resume(self, width, height, samples, state=None, sample_begin=0, rows=None, pixel0_seed=1, params=None):
+        """Progressive rendering (rtb_render_resume): samples [sample_begin, samples) of every pixel.  `state` (uint32
+        array [rows, width, 8]) is what an earlier call with samples == sample_begin returned; the returned state is
+        the one after `samples` samples.  accum / rgb are those of ONE call with `samples` samples, bit for bit."""
+        if params is None:
+            r0, r1 = rows if rows is not None else (0, height)
+            params = RenderParams(width, height, samples, r0, r1, pixel0_seed, sample_begin, 0)
+        n = lib().rtb_render_local_rows(C.byref(params))
+        if n < 0:
+            raise RtbError(RTB_ERR_INVALID, "bad render parameters")
+        if state is None:
+            if params.sample_begin > 0:
+                raise RtbError(RTB_ERR_INVALID, "sample_begin > 0 needs the pixel state of the earlier call")
+            state = np.zeros((n, params.width, PIXEL_STATE_BYTES // 4), np.uint32)
+        else:
+            state = np.ascontiguousarray(state, np.uint32).copy()
+            assert state.nbytes == lib().rtb_render_state_bytes(C.byref(params))
+        accum = np.empty((n, params.width, 3), np.float32)
+        rgb = np.empty((n, params.width, 3), np.uint8)
+        st = Stats()
+        _check(lib().rtb_render_resume(self.h, C.byref(params), _ptr(state), _ptr(accum), _ptr(rgb), C.byref(st)))
+        return dict(accum=accum, rgb=rgb, state=state, stats=st.as_dict())
+
+    def set_progress(self, fn):
+        """fn(percent) is called on the rendering thread while a frame renders (rtb_scene_set_progress); None: off."""
+        self._progress = PROGRESS_FN(lambda pct, _user: int(fn(pct) or 0)) if fn is not None else PROGRESS_FN()
+        _check(lib().rtb_scene_set_progress(self.h, self._progress, None))
 
     def render_device(self, params, d_accum=None, d_rgb8=None, d_counters=None, stream=0):
         """DEVICE output pointers (e.g. torch tensors), asynchronous on `stream` (a cudaStream_t handle)."""

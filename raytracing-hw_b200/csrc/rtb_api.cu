@@ -369,15 +369,19 @@ int rtb_render_global_row(const rtb_render_params *p, int lr) {
     return p->row_begin + ((lr / R) * p->interleave_count + p->interleave_index) * R + lr % R;
 }
 
-int rtb_render_device(rtb_scene *scene, const rtb_render_params *p, float *d_accum, uint8_t *d_rgb8, unsigned long long *d_counters,
-                      void *stream) {
+int rtb_render_resume_device(rtb_scene *scene, const rtb_render_params *p, void *d_pixel_state, float *d_accum, uint8_t *d_rgb8,
+                             unsigned long long *d_counters, void *stream) {
     if (!scene || !p) { rtb::set_error("rtb_render_device: null argument"); return RTB_ERR_INVALID; }
     const int local_rows = rtb_render_local_rows(p);
     if (local_rows < 0 || p->samples <= 0) {
         rtb::set_error("rtb_render_device: bad canvas / row range / interleave / sample count");
         return RTB_ERR_INVALID;
     }
-    if (p->sample_begin != 0) { rtb::set_error("rtb_render_device: sample_begin must be 0 (a pixel's samples share one sequential stream)"); return RTB_ERR_INVALID; }
+    if (p->sample_begin < 0 || p->sample_begin >= p->samples || (p->sample_begin > 0 && !d_pixel_state)) {
+        rtb::set_error("rtb_render_device: sample_begin must be 0, or the sample count of the pixel state handed to rtb_render_resume (< samples): "
+                       "a pixel's samples share one sequential stream");
+        return RTB_ERR_INVALID;
+    }
     RTB_CUDA(cudaSetDevice(scene->device));
     rtb::RenderLaunch L;
     L.width = p->width; L.height = p->height; L.samples = p->samples;
@@ -388,9 +392,15 @@ int rtb_render_device(rtb_scene *scene, const rtb_render_params *p, float *d_acc
     L.d_accum = d_accum; L.d_rgb8 = d_rgb8; L.d_counters = d_counters;
     L.count_tests = (p->flags & RTB_RENDER_COUNTERS) != 0 && d_counters != nullptr;
     L.cull_mode = (p->flags & RTB_RENDER_REFERENCE_CULL) ? RTB_CULL_REFERENCE : RTB_CULL_GLOBAL;
+    L.sample_begin = p->sample_begin;
+    L.d_pixel_state = (uint4 *) d_pixel_state;
     // Integrator: the wavefront (ray-queue) form unless the caller asks for the megakernel; RTB_CULL_REFERENCE only
     // exists as a megakernel (the queue traverses with global-best culling).
     const bool mega = (p->flags & (RTB_RENDER_REFERENCE_CULL | RTB_RENDER_MEGAKERNEL)) != 0 || scene->d.ray_depth < 1 || scene->d.ray_depth > 15;
+    if (mega && d_pixel_state) {
+        rtb::set_error("rtb_render_resume: the pixel state is kept by the wavefront integrator only (no RTB_RENDER_MEGAKERNEL / RTB_RENDER_REFERENCE_CULL)");
+        return RTB_ERR_INVALID;
+    }
     if (mega || local_rows == 0) {
         rtb::launch_render(scene->d, L, (cudaStream_t) stream);
         scene->launches += local_rows ? 1 : 0;
@@ -419,7 +429,28 @@ int rtb_render_device(rtb_scene *scene, const rtb_render_params *p, float *d_acc
     return RTB_OK;
 }
 
+int rtb_render_device(rtb_scene *scene, const rtb_render_params *p, float *d_accum, uint8_t *d_rgb8, unsigned long long *d_counters,
+                      void *stream) {
+    return rtb_render_resume_device(scene, p, nullptr, d_accum, d_rgb8, d_counters, stream);
+}
+
+int rtb_scene_set_progress(rtb_scene *scene, rtb_progress_fn fn, void *user) {
+    if (!scene) { rtb::set_error("rtb_scene_set_progress: null scene"); return RTB_ERR_INVALID; }
+    scene->wf_streams.progress = fn;
+    scene->wf_streams.progress_user = user;
+    return RTB_OK;
+}
+
+size_t rtb_render_state_bytes(const rtb_render_params *p) {
+    const int rows = p ? rtb_render_local_rows(p) : -1;
+    return rows < 0 ? 0 : (size_t) rows * (size_t) p->width * RTB_PIXEL_STATE_BYTES;
+}
+
 int rtb_render(rtb_scene *scene, const rtb_render_params *p, float *accum, uint8_t *rgb8, rtb_stats *stats) {
+    return rtb_render_resume(scene, p, nullptr, accum, rgb8, stats);
+}
+
+int rtb_render_resume(rtb_scene *scene, const rtb_render_params *p, void *state, float *accum, uint8_t *rgb8, rtb_stats *stats) {
     if (!scene || !p) { rtb::set_error("rtb_render: null argument"); return RTB_ERR_INVALID; }
     if (stats) std::memset(stats, 0, sizeof(*stats));
     RTB_CUDA(cudaSetDevice(scene->device));
@@ -427,8 +458,15 @@ int rtb_render(rtb_scene *scene, const rtb_render_params *p, float *accum, uint8
     if (local_rows < 0) { rtb::set_error("rtb_render: bad canvas / row range / interleave"); return RTB_ERR_INVALID; }
     const size_t npix = (size_t) local_rows * (size_t) p->width;
     const size_t accum_bytes = npix * 3 * sizeof(float), rgb_bytes = npix * 3;
+    const size_t state_bytes = state ? npix * RTB_PIXEL_STATE_BYTES : 0;
     const size_t rgb_off = (accum_bytes + 255) / 256 * 256, cnt_off = rgb_off + (rgb_bytes + 255) / 256 * 256;
-    int rc = ensure_stage(scene, cnt_off + 256);
+    const size_t state_off = cnt_off + 256;
+    if (state && p->sample_begin > 0 && npix > 0 && ((const uint32_t *) state)[3] != (uint32_t) p->sample_begin) {
+        rtb::set_error("rtb_render_resume: the pixel state holds " + std::to_string(((const uint32_t *) state)[3]) +
+                       " samples per pixel, sample_begin says " + std::to_string(p->sample_begin));
+        return RTB_ERR_INVALID;
+    }
+    int rc = ensure_stage(scene, state_off + state_bytes);
     if (rc != RTB_OK) return rc;
     char *base = (char *) scene->stage;
     float *d_accum = (float *) base;
@@ -438,9 +476,12 @@ int rtb_render(rtb_scene *scene, const rtb_render_params *p, float *accum, uint8
     RTB_CUDA(cudaMemsetAsync(d_cnt, 0, 48, st));
     RTB_CUDA(cudaEventRecord(scene->ev[0], st));
     const unsigned long long launches_before = scene->launches;
-    rc = rtb_render_device(scene, p, d_accum, rgb8 ? d_rgb : nullptr, d_cnt, st);
+    void *d_state = state ? (void *) (base + state_off) : nullptr;
+    if (state && p->sample_begin > 0) RTB_CUDA(cudaMemcpyAsync(d_state, state, state_bytes, cudaMemcpyHostToDevice, st));
+    rc = rtb_render_resume_device(scene, p, d_state, d_accum, rgb8 ? d_rgb : nullptr, d_cnt, st);
     if (rc != RTB_OK) return rc;
     RTB_CUDA(cudaEventRecord(scene->ev[1], st));
+    if (state && state_bytes) RTB_CUDA(cudaMemcpyAsync(state, d_state, state_bytes, cudaMemcpyDeviceToHost, st));
     if (accum && accum_bytes) RTB_CUDA(cudaMemcpyAsync(accum, d_accum, accum_bytes, cudaMemcpyDeviceToHost, st));
     if (rgb8 && rgb_bytes) RTB_CUDA(cudaMemcpyAsync(rgb8, d_rgb, rgb_bytes, cudaMemcpyDeviceToHost, st));
     unsigned long long c[6] = {0, 0, 0, 0, 0, 0};

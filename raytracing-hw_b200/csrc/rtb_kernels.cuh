@@ -27,6 +27,13 @@ struct RenderLaunch {
     unsigned long long *d_counters;     // 6 x u64 {rays, light queries, box, tri, light box, light tri} or null
     bool count_tests;                   // also count box / triangle tests (slower instantiation)
     int cull_mode;                      // RTB_CULL_*
+    // progressive rendering (wavefront integrator only, rtb_render_resume): the call renders samples
+    // [sample_begin, samples) of every pixel.  d_pixel_state: 2 x uint4 per local pixel {engine value, cached Marsaglia
+    // half (bits), has-cached flag, samples done}, {sum r, g, b (bits), 0}; read when sample_begin > 0, written (if not
+    // null) when a pixel has had its last sample.  A pixel's samples are one sequential engine stream
+    // (src/core/scene.cpp:34-42), so this is everything a later call needs to carry on bit for bit.
+    int sample_begin;
+    uint4 *d_pixel_state;
 };
 void launch_render(const DScene &sc, const RenderLaunch &p, cudaStream_t stream);
 // wavefront (ray-queue) integrator, rtb_wavefront.cu; `state` = wf_alloc_bytes() bytes of device memory
@@ -42,6 +49,10 @@ struct WfStreams {   // owned by the scene: one stream per slot group + fork / j
     cudaGraphExec_t graph_exec = nullptr;
     std::vector<unsigned char> graph_key;
     unsigned long long graph_launches = 0;   // kernels per replay
+    // progress line (rtb_scene_set_progress): called on the rendering thread with 0..100 while the frame's iterations
+    // complete (the reference's USE_CALLBACK build: src/main.cpp:8-20, scene.cpp:45-50)
+    int (*progress)(int, void *) = nullptr;
+    void *progress_user = nullptr;
 };
 void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *state, cudaStream_t stream, unsigned long long *launches,
                              std::vector<cudaEvent_t> *stage_events, WfStreams *aux);

@@ -14,7 +14,10 @@
 #include "rtb_wavefront.cuh"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdlib>
+#include <thread>
+#include <utility>
 #include <vector>
 #include "rtb_trace.cuh"
 
@@ -352,7 +355,7 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
     // samples x ray_depth iterations trace every ray a pixel can need when no ray is ever suspended; with suspension a
     // slot sometimes spends an iteration without finishing its ray, so a margin is enqueued up front and the live counts
     // are then read back (the one host synchronisation of a frame) until every group's list is empty
-    const long long base_iterations = (long long) p.samples * sc.ray_depth;
+    const long long base_iterations = (long long) (p.samples - p.sample_begin) * sc.ray_depth;
     const long long iterations = tail_steps > 0 ? base_iterations + base_iterations / 16 + 8 : base_iterations;
     const int period = 16;   // iterations between compactions
     // optional stage timing: events[2*it], events[2*it+1] bracket iteration it's k_wf_trace; events[2*iterations] ends the frame
@@ -366,6 +369,34 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
         }
         cudaEventRecord((*stage_events)[ev_i++], stream);
     };
+    // Progress line (rtb_scene_set_progress): events on the first group's stream every ~1 % of the planned iterations;
+    // once everything is enqueued the host polls them in order and calls back as they complete.
+    int (*const progress)(int, void *) = (aux && !stage_events) ? aux->progress : nullptr;
+    void *const progress_user = aux ? aux->progress_user : nullptr;
+    std::vector<std::pair<cudaEvent_t, int>> prog_ev;
+    const long long prog_stride = std::max<long long>(1, iterations / 100);
+    int prog_last = -1;
+    auto prog_call = [&](int pct) {
+        if (progress && pct != prog_last) { prog_last = pct; progress(pct, progress_user); }
+    };
+    auto prog_mark = [&](long long its_done, cudaStream_t st) {
+        if (!progress) return;
+        cudaEvent_t e;
+        if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) { cudaGetLastError(); return; }
+        cudaEventRecord(e, st);
+        prog_ev.emplace_back(e, (int) std::min<long long>(99, its_done * 100 / std::max<long long>(1, iterations)));
+    };
+    auto prog_drain = [&]() {
+        for (auto &pe : prog_ev) {
+            cudaError_t q;
+            while ((q = cudaEventQuery(pe.first)) == cudaErrorNotReady) std::this_thread::sleep_for(std::chrono::microseconds(200));
+            if (q != cudaSuccess) cudaGetLastError();
+            else prog_call(pe.second);
+            cudaEventDestroy(pe.first);
+        }
+        prog_ev.clear();
+    };
+    prog_call(0);
     auto run_iteration = [&](long long it) {
         for (int g = 0; g < G; ++g) {
             Group &q = grp[g];
@@ -441,8 +472,11 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
         }
         if (ok) {
             long long done = 0;
-            for (; done < n_graph_blocks; ++done)
+            const long long blocks_per_mark = std::max<long long>(1, n_graph_blocks / 100);
+            for (; done < n_graph_blocks; ++done) {
                 if (cudaGraphLaunch(aux->graph_exec, stream) != cudaSuccess) { cudaGetLastError(); break; }
+                if ((done + 1) % blocks_per_mark == 0) prog_mark((done + 1) * kBlockIts, stream);
+            }
             nl += aux->graph_launches * (unsigned long long) done;
             it0 = done * kBlockIts;
         }
@@ -450,7 +484,11 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
         cudaEventRecord(aux->fork, stream);
         for (int g = 0; g < G; ++g) cudaStreamWaitEvent(grp[g].st, aux->fork, 0);
     }
-    for (long long it = it0; it < iterations; ++it) run_iteration(it);
+    for (long long it = it0; it < iterations; ++it) {
+        run_iteration(it);
+        if ((it + 1) % prog_stride == 0) prog_mark(it + 1, grp[0].st);
+    }
+    prog_drain();
     auto join = [&]() {
         if (G <= 1) return;
         for (int g = 0; g < G; ++g) {
@@ -482,6 +520,10 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
     }
     mark();
     join();
+    if (progress) {   // (with a progress line the call returns when the frame is complete)
+        cudaStreamSynchronize(stream);
+        prog_call(100);
+    }
     if (stage_events) stage_events->resize(ev_i);   // (events beyond ev_i were created by an earlier, longer frame)
     if (launches) *launches += nl;
 }

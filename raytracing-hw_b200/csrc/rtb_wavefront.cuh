@@ -67,15 +67,25 @@ RTB_HD unsigned wf_init_slot(const DScene &sc, const RenderLaunch &p, const WfSt
     int px, lr, py;
     if (!wf_slot_pixel(p, slot, px, lr, py)) return slot | kSlotDone;
     Rng g;
-    const uint64_t seed = (uint64_t) py * (uint64_t) p.width + (uint64_t) px;
-    rng_seed(g, seed != 0 ? seed : (uint64_t) p.pixel0_seed);
+    float4 sum0 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.sample_begin > 0) {   // resume: the pixel's engine and sum as an earlier call left them
+        const size_t o = ((size_t) lr * p.width + px) * 2;
+        const uint4 a = p.d_pixel_state[o], b = p.d_pixel_state[o + 1];
+        g.x = a.x;
+        g.saved = u2f(a.y);
+        g.has_saved = (a.z & 1u) != 0u;
+        sum0 = make_float4(u2f(b.x), u2f(b.y), u2f(b.z), 0.f);
+    } else {
+        const uint64_t seed = (uint64_t) py * (uint64_t) p.width + (uint64_t) px;
+        rng_seed(g, seed != 0 ? seed : (uint64_t) p.pixel0_seed);
+    }
     const float ox = rng_pixel_offset(g);
     const float oy = rng_pixel_offset(g);
     // Camera::cast_in_pixel hands the un-normalised direction to Ray::Ray; store exactly that
     const V3 d = camera_dir(sc, px, py, p.width, p.height, ox, oy);
     wf_store_ray(w, slot, V3{sc.cam_pos[0], sc.cam_pos[1], sc.cam_pos[2]}, d);
-    w.ctl[slot] = make_uint4(g.x, f2u(g.saved), 0u, (g.has_saved ? 256u : 0u));
-    w.sum[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+    w.ctl[slot] = make_uint4(g.x, f2u(g.saved), (unsigned) p.sample_begin, (g.has_saved ? 256u : 0u));
+    w.sum[slot] = sum0;
     return slot;
 }
 
@@ -192,6 +202,11 @@ RTB_HD unsigned wf_shade_slot(const DScene &sc, const RenderLaunch &p, const WfS
                 p.d_rgb8[o] = resolve_channel(sum.x, normalizer);
                 p.d_rgb8[o + 1] = resolve_channel(sum.y, normalizer);
                 p.d_rgb8[o + 2] = resolve_channel(sum.z, normalizer);
+            }
+            if (p.d_pixel_state) {
+                const size_t so = ((size_t) lr * p.width + px) * 2;
+                p.d_pixel_state[so] = make_uint4(g.x, f2u(g.saved), g.has_saved ? 1u : 0u, (unsigned) sample);
+                p.d_pixel_state[so + 1] = make_uint4(f2u(sum.x), f2u(sum.y), f2u(sum.z), 0u);
             }
             entry = slot | kSlotDone;
         } else {

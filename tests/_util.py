@@ -117,6 +117,7 @@ def devsim():
         L.devsim_light_pdf.argtypes = [C.POINTER(rtb.SceneDesc), vp, C.c_size_t, vp]
         L.devsim_render.argtypes = [C.POINTER(rtb.SceneDesc), C.POINTER(rtb.RenderParams), vp, vp, vp]
         L.devsim_render_wavefront.argtypes = [C.POINTER(rtb.SceneDesc), C.POINTER(rtb.RenderParams), vp, vp, vp]
+        L.devsim_render_wavefront_resume.argtypes = [C.POINTER(rtb.SceneDesc), C.POINTER(rtb.RenderParams), vp, vp, vp, vp]
         L.devsim_trace_path.argtypes = [C.POINTER(rtb.SceneDesc), vp, vp, C.c_uint, vp, C.POINTER(C.c_uint)]
         _devsim = L
     return _devsim
@@ -172,6 +173,16 @@ def devsim_render(hs, width, height, samples, rows=None, pixel0_seed=1, referenc
     fn = devsim().devsim_render_wavefront if wavefront else devsim().devsim_render
     assert fn(C.byref(hs.desc), C.byref(p), _p(accum), _p(rgb), _p(cnt)) == 0, devsim().devsim_last_error()
     return dict(accum=accum, rgb=rgb, rays=int(cnt[0]), light_queries=int(cnt[1]), box_tests=int(cnt[2]), tri_tests=int(cnt[3]))
+
+
+def devsim_render_resume(hs, width, height, samples, state=None, sample_begin=0, pixel0_seed=1):
+    """the host build of the wavefront integrator with rtb_render_resume's per-pixel state"""
+    p = rtb.RenderParams(width, height, samples, 0, height, pixel0_seed, sample_begin, 0)
+    accum = np.empty((height, width, 3), np.float32)
+    rgb = np.empty((height, width, 3), np.uint8)
+    state = np.zeros((height, width, 8), np.uint32) if state is None else np.ascontiguousarray(state, np.uint32).copy()
+    assert devsim().devsim_render_wavefront_resume(C.byref(hs.desc), C.byref(p), _p(state), _p(accum), _p(rgb), None) == 0, devsim().devsim_last_error()
+    return dict(accum=accum, rgb=rgb, state=state)
 
 
 def devsim_trace_path(hs, origin, direction, seed):

@@ -192,7 +192,15 @@ int devsim_render(const rtb_scene_desc *desc, const rtb_render_params *p, float 
 
 // The wavefront integrator's per-slot steps (rtb_wavefront.cuh: wf_init_slot / wf_shade_slot -- the same functions the
 // k_wf_* kernels call) driven on host arrays, with the queue replaced by closest_hit_global per active slot.
+int devsim_render_wavefront_resume(const rtb_scene_desc *desc, const rtb_render_params *p, void *pixel_state, float *accum, uint8_t *rgb8,
+                                   unsigned long long *counters4);
 int devsim_render_wavefront(const rtb_scene_desc *desc, const rtb_render_params *p, float *accum, uint8_t *rgb8, unsigned long long *counters4) {
+    return devsim_render_wavefront_resume(desc, p, nullptr, accum, rgb8, counters4);
+}
+// samples [p->sample_begin, p->samples) with the per-pixel state of rtb_render_resume (32 bytes per local pixel; in when
+// sample_begin > 0, out when not null)
+int devsim_render_wavefront_resume(const rtb_scene_desc *desc, const rtb_render_params *p, void *pixel_state, float *accum, uint8_t *rgb8,
+                                   unsigned long long *counters4) {
     SimScene s;
     if (!make_scene(desc, s, g_err)) return 1;
     RenderLaunch L;
@@ -211,6 +219,9 @@ int devsim_render_wavefront(const rtb_scene_desc *desc, const rtb_render_params 
     }
     L.pixel0_seed = p->pixel0_seed;
     L.d_accum = accum; L.d_rgb8 = rgb8;
+    L.sample_begin = p->sample_begin;
+    L.d_pixel_state = (uint4 *) pixel_state;
+    if (p->sample_begin > 0 && !pixel_state) { g_err = "sample_begin > 0 without a pixel state"; return 3; }
     const unsigned n_slots = (unsigned) (((L.width + kWfTileW - 1) / kWfTileW) * ((L.local_rows + kWfTileH - 1) / kWfTileH) * 32);
     const int cap = std::max(1, s.d.ray_depth - 1);
     std::vector<float4> ray_a(n_slots), hit(n_slots), sum(n_slots), stk_e((size_t) n_slots * cap), stk_m((size_t) n_slots * cap);
@@ -224,7 +235,7 @@ int devsim_render_wavefront(const rtb_scene_desc *desc, const rtb_render_params 
     std::vector<unsigned> list(n_slots);
     for (unsigned i = 0; i < n_slots; ++i) list[i] = wf_init_slot(s.d, L, w, i);
     unsigned long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;
-    const long long iterations = (long long) p->samples * s.d.ray_depth;
+    const long long iterations = (long long) (p->samples - p->sample_begin) * s.d.ray_depth;
     for (long long it = 0; it < iterations; ++it) {
 #pragma omp parallel for schedule(dynamic, 64) reduction(+ : c0, c1, c2, c3)
         for (long long i = 0; i < (long long) n_slots; ++i) {

@@ -241,3 +241,20 @@ def test_big_leaves_and_exact_ties():
             assert np.array_equal(h[k], want[k]), (form, k)
     ordered = _util.devsim_closest_hit(hs, rays, rtb.CULL_REFERENCE)
     assert (ordered["box_tests"], ordered["tri_tests"]) == (want["box_tests"], want["tri_tests"])
+
+
+def test_wavefront_resume_is_bit_identical(host_scene):
+    """rtb_render_resume's contract on the host build of the wavefront integrator: a frame rendered in chunks of samples
+    through the 32-byte per-pixel state (engine, cached normal half, sum) = the frame rendered at once, bit for bit --
+    and every intermediate image is the one-shot image at that sample count"""
+    hs = host_scene("s6_1")
+    W, H = 24, 16
+    whole = _util.devsim_render_resume(hs, W, H, 7)
+    part = _util.devsim_render_resume(hs, W, H, 2)
+    assert np.array_equal(part["rgb"], _util.devsim_render(hs, W, H, 2, pixel0_seed=1, wavefront=True)["rgb"])
+    assert np.all(part["state"][..., 3] == 2)
+    part = _util.devsim_render_resume(hs, W, H, 3, state=part["state"], sample_begin=2)
+    assert np.array_equal(part["accum"], _util.devsim_render(hs, W, H, 3, pixel0_seed=1, wavefront=True)["accum"])
+    part = _util.devsim_render_resume(hs, W, H, 7, state=part["state"], sample_begin=3)
+    assert np.array_equal(part["accum"], whole["accum"]) and np.array_equal(part["rgb"], whole["rgb"])
+    assert np.array_equal(part["state"], whole["state"])

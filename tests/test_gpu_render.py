@@ -159,6 +159,86 @@ def test_cli_drop_in(tmp_path, host_scene):
     assert data[len(b"P6\n48 40\n255\n"):] == want.tobytes()
 
 
+@pytest.mark.parametrize("name,size,spp,cuts", [("s7_4", (200, 120), 24, (1, 9, 10)), ("sponza_small", (160, 90), 16, (5,)),
+                                                 ("s7_4", (1280, 720), 6, (2, 4))])
+def test_resume_is_bit_identical(name, size, spp, cuts, host_scene):
+    """rtb_render_resume: a frame rendered in chunks through the 32-byte per-pixel state (engine, cached normal half,
+    radiance sum) has the sums, bytes and final state of the frame rendered by one call -- and every intermediate image
+    is the one-call image at that sample count (the 1280x720 case runs in slot groups with graph replay)"""
+    W, H = size
+    sc = device_scene(host_scene(name))
+    whole = sc.render_resume(W, H, spp)
+    assert np.array_equal(whole["accum"], sc.render(W, H, spp)["accum"])
+    assert np.all(whole["state"][..., 3] == spp)
+    state, done, part = None, 0, None
+    for cut in list(cuts) + [spp]:
+        part = sc.render_resume(W, H, cut, state=state, sample_begin=done)
+        state, done = part["state"], cut
+        if cut == cuts[0]:
+            assert np.array_equal(part["rgb"], sc.render(W, H, cut)["rgb"])
+    assert np.array_equal(part["accum"], whole["accum"]) and np.array_equal(part["rgb"], whole["rgb"])
+    assert np.array_equal(part["state"], whole["state"])
+
+
+def test_resume_matches_host_state_machine_and_rejects_misuse(host_scene):
+    """the pixel state the GPU writes equals the one the host build of the same integrator writes; a state of the wrong
+    sample count, a missing state and the megakernel are refused"""
+    hs = host_scene("s6_1")
+    sc = device_scene(hs)
+    W, H = 24, 16
+    got = sc.render_resume(W, H, 3)
+    want = _util.devsim_render_resume(hs, W, H, 3)
+    assert np.array_equal(got["state"], want["state"]) and np.array_equal(got["accum"], want["accum"])
+    with pytest.raises(rtb.RtbError):
+        sc.render_resume(W, H, 8, state=got["state"], sample_begin=2)
+    with pytest.raises(rtb.RtbError):
+        sc.render_resume(W, H, 8, sample_begin=3)
+    with pytest.raises(rtb.RtbError):
+        sc.render_resume(W, H, 8, params=rtb.RenderParams(W, H, 8, 0, H, 1, 0, 4))   # RTB_RENDER_MEGAKERNEL
+
+
+def test_progress_callback(host_scene):
+    """rtb_scene_set_progress: 0 first, 100 last, never decreasing -- and the frame's bits do not change"""
+    sc = rtb.Scene(host_scene("s7_4"), 0)
+    want = sc.render(320, 200, 12)
+    seen = []
+    sc.set_progress(lambda pct: seen.append(pct))
+    got = sc.render(320, 200, 12)
+    sc.set_progress(None)
+    assert np.array_equal(got["accum"], want["accum"])
+    assert seen[0] == 0 and seen[-1] == 100 and seen == sorted(seen) and len(seen) >= 3
+    n = len(seen)
+    sc.render(320, 200, 2)
+    assert len(seen) == n
+
+
+def test_cli_progressive_and_checkpoint(tmp_path, host_scene):
+    """the CLI's RT_CHUNK / RT_CHECKPOINT / RT_PROGRESS knobs: a frame rendered 3 samples at a time, and a frame resumed
+    from the checkpoint of an interrupted run, are byte-identical to the one-call frame; the progress line has the
+    reference's USE_CALLBACK format"""
+    exe = os.path.join(_util.ROOT, "build", "solution")
+    scene, args = _util.scene_path("s7_4"), ["64", "40", "8"]
+    env = dict(os.environ, RT_GPUS="1")
+    one, chunks, resumed, ck = tmp_path / "one.ppm", tmp_path / "chunks.ppm", tmp_path / "resumed.ppm", tmp_path / "frame.ckpt"
+    r = subprocess.run([exe, scene] + args + [str(one)], capture_output=True, text=True, env=dict(env, RT_PROGRESS="1"))
+    assert r.returncode == 0, r.stderr
+    # (text mode turns the line's leading carriage return into a newline)
+    assert "   Render [          ] 0% (" in r.stdout and "   Render [**********] 100% (" in r.stdout and "ms) elapsed." in r.stdout
+    r = subprocess.run([exe, scene] + args + [str(chunks)], capture_output=True, text=True, env=dict(env, RT_CHUNK="3"))
+    assert r.returncode == 0, r.stderr
+    assert open(chunks, "rb").read() == open(one, "rb").read()
+    # an "interrupted" run: 5 of 8 samples, checkpoint kept (a frame of 5 samples asked for with a checkpoint file is
+    # complete and removes it, so write the state through the library instead)
+    sc = device_scene(host_scene("s7_4", 64, 40, 8))
+    part = sc.render_resume(64, 40, 5)
+    with open(ck, "wb") as f:
+        f.write(b"RTBCKPT1" + np.array([64, 40, 5, 1], np.int32).tobytes() + part["state"].tobytes())
+    r = subprocess.run([exe, scene] + args + [str(resumed)], capture_output=True, text=True, env=dict(env, RT_CHECKPOINT=str(ck)))
+    assert r.returncode == 0 and "resuming from" in r.stderr, r.stderr
+    assert open(resumed, "rb").read() == open(one, "rb").read()
+    assert not os.path.exists(ck)
+
+
 def test_full_size_properties(host_scene):
     """cfg2's canvas (1280x720) on its stand-in at a reduced spp, through size-independent properties: determinism
     (two launches, same bits), finite non-negative radiance, resolve of the sums equals the fused RGB8, and the
