@@ -253,16 +253,20 @@ unsigned wf_slots(const RenderLaunch &p) {
 // (before rays could be suspended, groups paid off from 1/2 frame down: they hid the tails of each other's launches;
 // with bounded tails their contention costs more than that until a launch is too small to fill the GPU.)
 // Default: one group down to 0.4 M slots, below that as many groups as bring a group down to ~0.26 M / 8 slots.
-int wf_groups(unsigned n_slots) {
+// Light scenes (a traversal set that sits in the L1s: the 36-triangle boxes of cfg2) are the exception: their queue
+// kernel is short and not ALU-bound, the frame is as much shade as trace, and a second group overlaps the two
+// (profiles/r01m_groups_light_scene_sweep.txt: 1280x720 590 / 657 / 650 / 636 with 1 / 2 / 3 / 4 groups; 1920x1080
+// 605 / 654 / 652 with 1 / 2 / 4; 640x360 461 / 512 / 527 with 1 / 2 / 4).
+int wf_groups(unsigned n_slots, bool light_scene) {
     static const int forced = [] {
         int g = 0;
         if (const char *e = std::getenv("RTB_WF_GROUPS")) g = std::max(1, std::min(kWfMaxGroups, std::atoi(e)));
         return g;
     }();
     if (forced) return forced;
-    if (n_slots >= 400000u) return 1;
+    if (n_slots >= 400000u) return light_scene ? 2 : 1;
     const unsigned g = ((2u << 20) + n_slots / 2) / std::max(1u, n_slots);
-    return (int) std::max(1u, std::min(8u, g));
+    return (int) std::max(1u, std::min(light_scene ? 4u : 8u, g));
 }
 
 // Slot groups.  The slots are cut into up to kWfMaxGroups contiguous groups, each with its own active list, queue
@@ -281,7 +285,8 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
     unsigned long long nl = 0;
 
     // a group needs enough slots to fill the persistent queue kernel a few times over
-    int G = (stage_events || !aux) ? 1 : wf_groups(n_slots);
+    const bool light_scene = (size_t) sc.bvh.n_internal * sizeof(DNode) + (size_t) sc.bvh.n_tris * kTriStride * sizeof(float4) <= (64u << 10);
+    int G = (stage_events || !aux) ? 1 : wf_groups(n_slots, light_scene);
     while (G > 1 && n_slots / (unsigned) G < 16u * 1024u) --G;
     struct Group {
         unsigned begin, count, n_blocks, block_off;
