@@ -28,6 +28,7 @@ ABI_SYMBOLS = [
     "rtb_closest_hit", "rtb_closest_hit_device", "rtb_light_pdf", "rtb_measure_l2",
     "rtb_render", "rtb_render_device", "rtb_resolve_device", "rtb_render_local_rows", "rtb_render_global_row",
     "rtb_render_resume", "rtb_render_resume_device", "rtb_render_state_bytes", "rtb_scene_set_progress",
+    "rtb_release_cached_memory",
     "rtb_write_ppm",
 ]
 
@@ -114,6 +115,8 @@ def lib():
         L.rtb_render_device.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.rtb_render_resume.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(Stats)]
         L.rtb_render_resume_device.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.rtb_release_cached_memory.argtypes = []
+        L.rtb_release_cached_memory.restype = None
         L.rtb_render_state_bytes.argtypes = [C.POINTER(RenderParams)]
         L.rtb_render_state_bytes.restype = C.c_size_t
         L.rtb_scene_set_progress.argtypes = [C.c_void_p, PROGRESS_FN, C.c_void_p]
@@ -347,6 +350,11 @@ class Scene:
     def render_device(self, params, d_accum=None, d_rgb8=None, d_counters=None, stream=0):
         """DEVICE output pointers (e.g. torch tensors), asynchronous on `stream` (a cudaStream_t handle)."""
         _check(lib().rtb_render_device(self.h, C.byref(params), _ptr(d_accum), _ptr(d_rgb8), _ptr(d_counters), C.c_void_p(stream)))
+
+
+def release_cached_memory():
+    """hand the device blocks kept from destroyed scenes back to the driver (rtb_release_cached_memory)"""
+    lib().rtb_release_cached_memory()
 
 
 def measure_l2(device=0, nbytes=32 << 20):

@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstring>
 #include <string>
+#include <mutex>
 #include <thread>
 #include <vector>
 
@@ -27,10 +28,94 @@ void set_error(const std::string &e);
 
 constexpr unsigned kQueueHeads = 64;
 
+// Device blocks of destroyed scenes (scene arena, path state, staging) are kept -- a few, bounded -- and handed to the
+// next scene that asks for a block of about that size.  A frame server that uploads a scene per frame otherwise pays
+// cudaMalloc / cudaFree of ~1 GB per frame: cudaFree alone was seen at 0.2 - 1.1 s (profiles/r01m_e2e_probe.txt).
+// RTB_BLOCK_CACHE_MB: the most the cache keeps (default 4096; 0: every block goes straight back to the driver).
+namespace rtb {
+namespace {
+struct BlockCache {
+    struct Block { int device; void *p; size_t bytes; };
+    std::mutex mu;
+    std::vector<Block> blocks;   // oldest first
+    size_t total = 0;
+    size_t limit() {
+        static const size_t v = [] {
+            const char *e = std::getenv("RTB_BLOCK_CACHE_MB");
+            return (size_t) (e ? std::max(0, std::atoi(e)) : 4096) << 20;
+        }();
+        return v;
+    }
+    // smallest kept block of this device that holds `bytes` without wasting more than half of itself
+    cudaError_t acquire(int device, size_t bytes, void **out, size_t *got) {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            int best = -1;
+            for (int i = 0; i < (int) blocks.size(); ++i) {
+                const Block &b = blocks[(size_t) i];
+                if (b.device != device || b.bytes < bytes || b.bytes > bytes + bytes / 2 + (1u << 20)) continue;
+                if (best < 0 || b.bytes < blocks[(size_t) best].bytes) best = i;
+            }
+            if (best >= 0) {
+                *out = blocks[(size_t) best].p;
+                *got = blocks[(size_t) best].bytes;
+                total -= *got;
+                blocks.erase(blocks.begin() + best);
+                return cudaSuccess;
+            }
+        }
+        *got = bytes;
+        cudaError_t e = cudaMalloc(out, bytes);
+        if (e != cudaSuccess) {   // out of memory with blocks parked here: give them back and try once more
+            cudaGetLastError();
+            trim(device);
+            e = cudaMalloc(out, bytes);
+        }
+        return e;
+    }
+    // the caller guarantees that no queued work uses the block any more
+    void release(int device, void *p, size_t bytes) {
+        if (!p) return;
+        std::vector<Block> drop;
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            if (bytes > limit()) drop.push_back(Block{device, p, bytes});
+            else {
+                blocks.push_back(Block{device, p, bytes});
+                total += bytes;
+                while (total > limit() || blocks.size() > 8) {
+                    drop.push_back(blocks.front());
+                    total -= blocks.front().bytes;
+                    blocks.erase(blocks.begin());
+                }
+            }
+        }
+        for (const Block &b : drop) { cudaSetDevice(b.device); cudaFree(b.p); }
+        if (!drop.empty()) cudaSetDevice(device);
+    }
+    void trim(int device) {   // device < 0: every device
+        std::vector<Block> drop;
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            for (size_t i = 0; i < blocks.size();) {
+                if (device < 0 || blocks[i].device == device) { drop.push_back(blocks[i]); total -= blocks[i].bytes; blocks.erase(blocks.begin() + (long) i); }
+                else ++i;
+            }
+        }
+        int cur = 0;
+        cudaGetDevice(&cur);
+        for (const Block &b : drop) { cudaSetDevice(b.device); cudaFree(b.p); }
+        cudaSetDevice(cur);
+    }
+};
+BlockCache g_blocks;
+}  // namespace
+}  // namespace rtb
+
 struct rtb_scene {
     int device = 0;
     rtb::DScene d;
-    std::vector<void *> allocs;
+    std::vector<std::pair<void *, size_t>> allocs;   // blocks from rtb::g_blocks
     size_t traversal_bytes = 0;
     size_t upload_bytes = 0;
     unsigned *queue_heads = nullptr;   // kQueueHeads ray-queue cursors, rotated per launch (stream-ordered memset)
@@ -50,9 +135,10 @@ struct rtb_scene {
     bool stage_events_valid = false;
     ~rtb_scene() {
         cudaSetDevice(device);
-        for (void *p : allocs) cudaFree(p);
-        if (stage) cudaFree(stage);
-        if (wf_state) cudaFree(wf_state);
+        cudaDeviceSynchronize();   // nothing queued may still use the blocks that go back to the cache
+        for (auto &a : allocs) rtb::g_blocks.release(device, a.first, a.second);
+        rtb::g_blocks.release(device, stage, stage_bytes);
+        rtb::g_blocks.release(device, wf_state, wf_bytes);
         for (auto &e : stage_events) cudaEventDestroy(e);
         if (wf_streams.graph_exec) cudaGraphExecDestroy(wf_streams.graph_exec);
         if (wf_streams.graph) cudaGraphDestroy(wf_streams.graph);
@@ -87,8 +173,9 @@ class Uploader {
     int alloc(rtb_scene *sc) {
         for (auto &p : pieces_) *p.dst = nullptr;
         if (total_ == 0) return RTB_OK;
-        RTB_CUDA(cudaMalloc(&base_, total_));
-        sc->allocs.push_back(base_);
+        size_t got = 0;
+        RTB_CUDA(rtb::g_blocks.acquire(sc->device, total_, &base_, &got));
+        sc->allocs.emplace_back(base_, got);
         for (auto &p : pieces_) if (p.bytes) *p.dst = (char *) base_ + p.off;
         return RTB_OK;
     }
@@ -165,11 +252,12 @@ class Uploader {
 
 int ensure_stage(rtb_scene *sc, size_t bytes) {
     if (sc->stage_bytes >= bytes) return RTB_OK;
-    if (sc->stage) cudaFree(sc->stage);
+    if (sc->stage) { RTB_CUDA(cudaDeviceSynchronize()); rtb::g_blocks.release(sc->device, sc->stage, sc->stage_bytes); }
     sc->stage = nullptr;
     sc->stage_bytes = 0;
-    RTB_CUDA(cudaMalloc(&sc->stage, bytes));
-    sc->stage_bytes = bytes;
+    size_t got = 0;
+    RTB_CUDA(rtb::g_blocks.acquire(sc->device, bytes, &sc->stage, &got));
+    sc->stage_bytes = got;
     return RTB_OK;
 }
 
@@ -408,11 +496,12 @@ int rtb_render_resume_device(rtb_scene *scene, const rtb_render_params *p, void 
         const size_t need = rtb::wf_alloc_bytes(rtb::wf_slots(L), std::max(1, scene->d.ray_depth - 1), scene->d.bvh.max_depth);
         if (scene->wf_bytes < need) {
             // the previous state may still be in use by work queued on a caller's stream
-            if (scene->wf_state) { RTB_CUDA(cudaDeviceSynchronize()); cudaFree(scene->wf_state); }
+            if (scene->wf_state) { RTB_CUDA(cudaDeviceSynchronize()); rtb::g_blocks.release(scene->device, scene->wf_state, scene->wf_bytes); }
             scene->wf_state = nullptr;
             scene->wf_bytes = 0;
-            RTB_CUDA(cudaMalloc(&scene->wf_state, need));
-            scene->wf_bytes = need;
+            size_t got = 0;
+            RTB_CUDA(rtb::g_blocks.acquire(scene->device, need, &scene->wf_state, &got));
+            scene->wf_bytes = got;
         }
         const bool timed = (p->flags & RTB_RENDER_STAGE_TIMES) != 0;
         if (!scene->wf_streams_ok) {
@@ -502,6 +591,8 @@ int rtb_render_resume(rtb_scene *scene, const rtb_render_params *p, void *state,
     }
     return RTB_OK;
 }
+
+void rtb_release_cached_memory(void) { rtb::g_blocks.trim(-1); }
 
 unsigned long long rtb_scene_launches(const rtb_scene *scene) { return scene ? scene->launches : 0ull; }
 

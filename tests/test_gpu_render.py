@@ -239,6 +239,26 @@ def test_cli_progressive_and_checkpoint(tmp_path, host_scene):
     assert not os.path.exists(ck)
 
 
+def test_scene_blocks_are_reused_across_scenes(host_scene):
+    """device blocks of a destroyed scene go to the next one (rtb_release_cached_memory hands them back): scenes created,
+    rendered and destroyed in turn -- of different sizes, so that blocks are reused with stale contents -- give the
+    bits of a scene on fresh memory"""
+    small, big = host_scene("s6_1"), host_scene("sponza_small")
+    rtb.release_cached_memory()
+    want = {}
+    for name, hs in (("small", small), ("big", big)):
+        sc = rtb.Scene(hs, 0)
+        want[name] = sc.render(160, 96, 4)["accum"]
+        sc.close()
+        rtb.release_cached_memory()
+    for name, hs in (("big", big), ("small", small), ("small", small), ("big", big), ("big", big)):
+        sc = rtb.Scene(hs, 0)
+        assert np.array_equal(sc.render(160, 96, 4)["accum"], want[name]), name
+        assert np.array_equal(sc.render(200, 120, 2)["rgb"], sc.render(200, 120, 2)["rgb"])
+        sc.close()
+    rtb.release_cached_memory()
+
+
 def test_full_size_properties(host_scene):
     """cfg2's canvas (1280x720) on its stand-in at a reduced spp, through size-independent properties: determinism
     (two launches, same bits), finite non-negative radiance, resolve of the sums equals the fused RGB8, and the
