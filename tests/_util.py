@@ -175,12 +175,17 @@ def devsim_render(hs, width, height, samples, rows=None, pixel0_seed=1, referenc
     return dict(accum=accum, rgb=rgb, rays=int(cnt[0]), light_queries=int(cnt[1]), box_tests=int(cnt[2]), tri_tests=int(cnt[3]))
 
 
-def devsim_render_resume(hs, width, height, samples, state=None, sample_begin=0, pixel0_seed=1):
-    """the host build of the wavefront integrator with rtb_render_resume's per-pixel state"""
+def devsim_render_resume(hs, width, height, samples, state=None, sample_begin=0, pixel0_seed=1, interleave=None):
+    """the host build of the wavefront integrator with rtb_render_resume's per-pixel state (interleave: (count, index,
+    rows) of the multi-GPU row-block split; buffers then hold the call's local rows)"""
     p = rtb.RenderParams(width, height, samples, 0, height, pixel0_seed, sample_begin, 0)
-    accum = np.empty((height, width, 3), np.float32)
-    rgb = np.empty((height, width, 3), np.uint8)
-    state = np.zeros((height, width, 8), np.uint32) if state is None else np.ascontiguousarray(state, np.uint32).copy()
+    n_rows = height
+    if interleave is not None:
+        p.interleave_count, p.interleave_index, p.interleave_rows = interleave
+        n_rows = rtb.lib().rtb_render_local_rows(C.byref(p))
+    accum = np.empty((n_rows, width, 3), np.float32)
+    rgb = np.empty((n_rows, width, 3), np.uint8)
+    state = np.zeros((n_rows, width, 8), np.uint32) if state is None else np.ascontiguousarray(state, np.uint32).copy()
     assert devsim().devsim_render_wavefront_resume(C.byref(hs.desc), C.byref(p), _p(state), _p(accum), _p(rgb), None) == 0, devsim().devsim_last_error()
     return dict(accum=accum, rgb=rgb, state=state)
 

@@ -1,6 +1,8 @@
 """CPU-side check of the restated device arithmetic: the device headers (raytracing-hw_b200/csrc/*.cuh) compiled
 for the host by nvcc (tests/devsim/) against the reference's golden answers.  This is NOT the parity proof of the
 CUDA path (that is tests/test_gpu_*.py, on the B200) -- it catches restatement errors where no GPU exists."""
+import ctypes as C
+
 import numpy as np
 import pytest
 
@@ -258,3 +260,30 @@ def test_wavefront_resume_is_bit_identical(host_scene):
     part = _util.devsim_render_resume(hs, W, H, 7, state=part["state"], sample_begin=3)
     assert np.array_equal(part["accum"], whole["accum"]) and np.array_equal(part["rgb"], whole["rgb"])
     assert np.array_equal(part["state"], whole["state"])
+
+
+def test_wavefront_resume_across_a_different_split(host_scene):
+    """the per-pixel state is indexed by the call's local rows: a frame started on a 3-way row-block split (3 GPUs),
+    its states merged into global row order (what the CLI's checkpoint file holds), carries on as one range -- and the
+    other way round -- with the bits of the one-call frame"""
+    hs = host_scene("s6_1")
+    W, H, R = 24, 40, 8
+    whole = _util.devsim_render_resume(hs, W, H, 5)
+    p = rtb.RenderParams(W, H, 2, 0, H, 1, 0, 0)
+    full = np.zeros((H, W, 8), np.uint32)
+    for idx in range(3):
+        p.interleave_count, p.interleave_index, p.interleave_rows = 3, idx, R
+        part = _util.devsim_render_resume(hs, W, H, 2, interleave=(3, idx, R))
+        for lr in range(part["state"].shape[0]):
+            full[rtb.lib().rtb_render_global_row(C.byref(p), lr)] = part["state"][lr]
+    assert np.array_equal(full, _util.devsim_render_resume(hs, W, H, 2)["state"])
+    rest = _util.devsim_render_resume(hs, W, H, 5, state=full, sample_begin=2)
+    assert np.array_equal(rest["accum"], whole["accum"]) and np.array_equal(rest["state"], whole["state"])
+    # and back onto a 2-way split
+    p2 = rtb.RenderParams(W, H, 5, 0, H, 1, 2, 0)
+    for idx in range(2):
+        p2.interleave_count, p2.interleave_index, p2.interleave_rows = 2, idx, R
+        n = rtb.lib().rtb_render_local_rows(C.byref(p2))
+        rows = [rtb.lib().rtb_render_global_row(C.byref(p2), lr) for lr in range(n)]
+        part = _util.devsim_render_resume(hs, W, H, 5, state=full[rows], sample_begin=2, interleave=(2, idx, R))
+        assert np.array_equal(part["accum"], whole["accum"][rows]) and np.array_equal(part["rgb"], whole["rgb"][rows])
