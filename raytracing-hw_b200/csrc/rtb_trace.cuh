@@ -89,7 +89,7 @@ struct LaneTraversal {
         s2 = stack;
         s2[0] = make_int2(kDoneLink, (int) f2u(-1.f));   // the sentinel is never culled
         s2[kUvSlot] = make_int2(0, 0);
-        rn = 0;
+        clear3();
     }
     // form 3 keeps what only the end of a ray needs out of the registers (the 48 / 56-register budgets of 10 / 9 CTAs
     // per SM): the barycentrics of the best hit live in a fixed local-memory slot above the stack (one predicated 64-bit
@@ -103,9 +103,14 @@ struct LaneTraversal {
     // words across the lanes, so a lane's 8-byte entry costs 2 sectors = 2 LSU wavefronts per LANE at divergent
     // depths: pushes and pops were 36 % of the LSU data-pipe work of the trace kernel, the unit that bounds it at 86 %
     // of peak (profiles/r01m_k_wf_trace_summary.txt).  kRing == 0: no ring, everything in the array.
-    static constexpr int kRing = RING;
+    // RING == -1: no ring, but the TOP entry of the stack is kept in registers (`top`; entries [0, sp - 1) in the array):
+    // a pop then needs one local load (the second entry) instead of two, and the entry that becomes the new top is
+    // either that one or is fetched off the critical path.
+    static constexpr bool kTop = RING < 0;
+    static constexpr int kRing = RING > 0 ? RING : 0;
     static_assert((kRing & (kRing - 1)) == 0, "the ring size is a power of two");
     int rn;                                                // entries in the ring
+    int2 top;                                              // kTop: entry sp - 1
 #ifndef __CUDA_ARCH__
     int2 host_ring[kRing > 0 ? kRing : 1];
 #endif
@@ -117,8 +122,16 @@ struct LaneTraversal {
         return host_ring[i & (kRing - 1)];
 #endif
     }
+    RTB_HD void clear3() {   // an empty stack: the sentinel only (entry 0 of the array always holds it)
+        sp = 1;
+        rn = 0;
+        top = make_int2(kDoneLink, (int) f2u(-1.f));
+    }
     RTB_HD void push3(const int2 e) {
-        if (kRing > 0) {
+        if (kTop) {
+            s2[sp - 1] = top;
+            top = e;
+        } else if (kRing > 0) {
             int2 &slot = ring_at(sp);
             if (rn == kRing) s2[sp - kRing] = slot;       // the oldest entry makes room
             else ++rn;
@@ -129,7 +142,7 @@ struct LaneTraversal {
         ++sp;
     }
     // entry i of the stack wherever it lives (suspending)
-    RTB_HD int2 entry3(int i) { return (kRing > 0 && i >= sp - rn) ? ring_at(i) : s2[i]; }
+    RTB_HD int2 entry3(int i) { return (kTop && i == sp - 1) ? top : (kRing > 0 && i >= sp - rn) ? ring_at(i) : s2[i]; }
     RTB_HD void finish3() {
         const int2 uv = s2[kUvSlot];
         best.u = u2f((uint32_t) uv.x);
@@ -156,6 +169,7 @@ struct LaneTraversal {
         s2[kUvSlot] = rec[4];
         for (int i = 0; i < sp; ++i) s2[i] = rec[kSuspHeader + i];
         rn = 0;
+        top = rec[kSuspHeader + sp - 1];
         omax = ray_omax(r);
         sgn = (r.d[0] > 0.f ? 1u : 0u) | (r.d[1] > 0.f ? 2u : 0u) | (r.d[2] > 0.f ? 4u : 0u);
     }
@@ -264,7 +278,10 @@ struct LaneTraversal {
         if (link == kPopLink) {
             const int i1 = sp - 1, i2 = sp >= 2 ? sp - 2 : 0;
             int2 e1, e2;
-            if (kRing > 0) {
+            if (kTop) {
+                e1 = top;
+                e2 = s2[i2];
+            } else if (kRing > 0) {
                 e1 = ring_at(i1);
                 e2 = ring_at(i2);
                 if (rn < 1) e1 = s2[i1];
@@ -277,6 +294,10 @@ struct LaneTraversal {
             link = k1 ? e1.x : (k2 ? e2.x : kPopLink);
             sp = k1 ? i1 : i2;
             if (kRing > 0) { rn -= k1 ? 1 : 2; rn = rn < 0 ? 0 : rn; }
+            if (kTop) {
+                top = e2;                                   // k1: the second entry is the new top
+                if (!k1) top = s2[i2 >= 1 ? i2 - 1 : 0];    // both consumed: the one below (not needed before the next pop / push)
+            }
             if (link == kDoneLink) sp = 1;                 // (the sentinel is entry 0 of the array, never in the ring)
         }
         if ((unsigned) link - 0x80000000u < 0x0FFFFFFEu) {   // a leaf of more than 7 triangles (rare): 7 now, the rest deferred
@@ -435,8 +456,7 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
                     suspend(tag, L);
                     have_ray = false;
                     L.link = kDoneLink;
-                    L.sp = 1;
-                    L.rn = 0;
+                    L.clear3();
                 } else {
                     budget = 16;
                 }

@@ -114,7 +114,8 @@ int devsim_closest_hit(const rtb_scene_desc *desc, const float *rays6, size_t n,
 
 // The queue kernels' per-lane state machine (rtb_trace.cuh: LaneTraversal, bounded branch-free pops) on the host.
 // schedule_seed selects the form: 0..2 the first form; 3 form 3 (one pop site per step); 4 / 5 form 3 with a 2- / 8-entry
-// ring on top of the stack; 100 + n form 3 suspended every n steps; 10000 + n the same with the 2-entry ring.
+// ring on top of the stack; 6 form 3 with the top entry in registers; 100 + n form 3 suspended every n steps; 10000 + n
+// the same with the 2-entry ring; 20000 + n the same with the top entry in registers.
 int devsim_closest_hit_lane(const rtb_scene_desc *desc, const float *rays6, size_t n, unsigned schedule_seed, int32_t *id, float *t,
                             float *u, float *v, unsigned long long *counters2) {
     SimScene s;
@@ -125,8 +126,10 @@ int devsim_closest_hit_lane(const rtb_scene_desc *desc, const float *rays6, size
         Counters c = {0, 0};
         Hit best;
         const float *ray6 = rays6 + i * 6;
-        if (schedule_seed >= 10000u) best = lane_form3<2>(s.d.bvh, ray6, (int) (schedule_seed - 10000u), c);
+        if (schedule_seed >= 20000u) best = lane_form3<-1>(s.d.bvh, ray6, (int) (schedule_seed - 20000u), c);
+        else if (schedule_seed >= 10000u) best = lane_form3<2>(s.d.bvh, ray6, (int) (schedule_seed - 10000u), c);
         else if (schedule_seed >= 100u) best = lane_form3<0>(s.d.bvh, ray6, (int) (schedule_seed - 100u), c);
+        else if (schedule_seed == 6u) best = lane_form3<-1>(s.d.bvh, ray6, 0, c);
         else if (schedule_seed == 5u) best = lane_form3<8>(s.d.bvh, ray6, 0, c);
         else if (schedule_seed == 4u) best = lane_form3<2>(s.d.bvh, ray6, 0, c);
         else if (schedule_seed == 3u) best = lane_form3<0>(s.d.bvh, ray6, 0, c);

@@ -76,11 +76,12 @@ def test_lane_form3_suspend_resume(name, every, host_scene):
 
 
 @pytest.mark.parametrize("name", SCENES)
-@pytest.mark.parametrize("form", [4, 5, 10001, 10007])
+@pytest.mark.parametrize("form", [4, 5, 6, 10001, 10007, 20001, 20007])
 def test_lane_form3_stack_ring(name, form, host_scene):
     """the top of the form-3 stack in a ring (what the batched queue kernel keeps in shared memory; LaneTraversal::push3 /
     pre3 / entry3) with the array as backing store: a 2-entry ring overflows and refills all the time, an 8-entry one
-    rarely; alone and combined with suspend / resume.  Same tests, same answers as the plain array."""
+    rarely; alone and combined with suspend / resume; and the variant with the top entry in registers (6, 2000x).  Same
+    tests, same answers as the plain array."""
     g = _util.load_golden(name)
     hs = host_scene(name)
     rays = np.concatenate([_util.box_rays(g["root_box"], 4096, seed=1000), _util.edge_rays(hs, g["root_box"], 4096, seed=78)])
