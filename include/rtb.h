@@ -101,6 +101,16 @@ typedef struct rtb_render_params {
      * this call renders the blocks b with b % interleave_count == interleave_index and writes them COMPACTLY, in block
      * order, into accum / rgb8 (rtb_render_local_rows() rows).  interleave_count <= 1: every row, as one range.        */
     int32_t interleave_count, interleave_index, interleave_rows;
+    /* sample-range split (SURVEY section 8e "optional sample-range split"; statistically equivalent to, NOT bit-identical
+     * with, the reference's stream).  substreams = K > 1: every pixel owns K independent engine streams; stream k is
+     * seeded with k*width*height + (j*width + i) -- the seed the reference would give a pixel of a K times taller canvas
+     * (src/core/scene.cpp:34) -- and takes samples [k*samples/K, (k+1)*samples/K) of the pixel; the K sums are folded in
+     * k order into the pixel's sum (src/core/scene.cpp:42).  Stream 0 of a pixel is the reference's own stream.  A
+     * call renders streams [substream_begin, substream_end) (0,0 = all K); a call that does not hold all K streams
+     * returns PARTIAL sums in accum (to be added to the other calls' -- across GPUs: rtb_render_dist) and must pass
+     * rgb8 == NULL.  Wavefront integrator only; not combinable with rtb_render_resume.  0 or 1: one stream per pixel,
+     * the reference's (bit-exact mode, the default).                                                                   */
+    int32_t substreams, substream_begin, substream_end;
 } rtb_render_params;
 
 /* number of rows a call with these parameters renders (and its output buffers hold); -1 on invalid parameters */
@@ -236,6 +246,45 @@ typedef int (*rtb_progress_fn)(int percent, void *user);
 int rtb_scene_set_progress(rtb_scene *scene, rtb_progress_fn fn, void *user);
 /* resolve only (src/core/scene.cpp:54-63): d_accum (n_pixels x 3 sums) -> d_rgb8 */
 int rtb_resolve_device(const float *d_accum, size_t n_pixels, int samples, uint8_t *d_rgb8, void *stream);
+
+/* ---- multi-GPU: the partition of Scene::render over the GPUs of one box and the combine on rank 0 ------
+ * The reference renders with one OpenMP loop (src/core/scene.cpp:31) and has no exchange step; the seam is main()'s
+ * `render()` followed by `draw_into()` (src/main.cpp:53-57).  One RANK per GPU -- a process (bench.py under torchrun)
+ * or a thread (rtb_render_multi, the CLI) -- and one communicator per rank over NCCL (loaded with dlopen at the first
+ * call; librtb.so does not link it):
+ *   rank 0: rtb_comm_unique_id(id); hand the RTB_UNIQUE_ID_BYTES bytes to every rank by any means;
+ *   all   : rtb_comm_create(id, world, rank, device, &comm);   (collective, like ncclCommInitRank)
+ *   all   : rtb_render_dist[_device](scene, comm, frame, split, ...)  per frame (collective).
+ * `frame` describes the WHOLE frame (width, height, samples, pixel0_seed, flags; row range and interleave index are
+ * set per rank by the call; interleave_rows, when > 0, is the block height of the tile split; substreams, when larger
+ * than the number of ranks, is the K of the sample split).
+ *   RTB_SPLIT_TILE  : interleaved row blocks, block b on rank b % world; every pixel keeps its own engine stream, the
+ *                     frame is bit-identical to the one-GPU frame.  Combine: ncclSend / ncclRecv of the finished RGB8 rows
+ *                     to rank 0 + one kernel that puts them in place.
+ *   RTB_SPLIT_SAMPLE: every rank renders the whole canvas with its share of K = max(substreams, world) engine streams per
+ *                     pixel (see rtb_render_params::substreams): statistically equivalent to the reference's stream, not
+ *                     bit-identical.  Combine: ncclReduce(sum) of the fp32 partial sums to rank 0, resolve (src/core/scene.cpp:54-63)
+ *                     behind it.  A frame is spp/world dependent samples long on every GPU whatever the canvas size.
+ * comm == NULL: one rank.  Results (d_rgb8_root / d_accum_root: the whole frame) are written on rank 0 only; d_accum_root
+ * is available with the sample split only.  d_counters as in rtb_render_device, per rank.                                   */
+#define RTB_UNIQUE_ID_BYTES 128
+#define RTB_SPLIT_TILE 0
+#define RTB_SPLIT_SAMPLE 1
+typedef struct rtb_comm rtb_comm;
+int rtb_comm_unique_id(void *id);
+int rtb_comm_create(const void *id, int world, int rank, int device, rtb_comm **out);
+void rtb_comm_destroy(rtb_comm *comm);
+int rtb_comm_world(const rtb_comm *comm);
+int rtb_comm_rank(const rtb_comm *comm);
+/* the rtb_render_params rank `rank` of `world` renders for `frame` under `split` (what rtb_render_dist passes to rtb_render_device) */
+int rtb_dist_rank_params(const rtb_render_params *frame, int split, int world, int rank, rtb_render_params *out);
+int rtb_render_dist_device(rtb_scene *scene, rtb_comm *comm, const rtb_render_params *frame, int split, float *d_accum_root,
+                           uint8_t *d_rgb8_root, unsigned long long *d_counters, void *stream);
+/* same with a HOST image on rank 0 (one device->host copy of the finished frame); stats per rank */
+int rtb_render_dist(rtb_scene *scene, rtb_comm *comm, const rtb_render_params *frame, int split, uint8_t *rgb8_root, rtb_stats *stats);
+/* one process, one thread per device: scenes[r] (on any n distinct devices) renders rank r's share; the frame arrives in
+ * rgb8 (host).  Communicators are created on the first call and kept.  stats: sums over the ranks (kernel_ms: the longest). */
+int rtb_render_multi(rtb_scene *const *scenes, int n, const rtb_render_params *frame, int split, uint8_t *rgb8, rtb_stats *stats);
 
 /* Canvas::write_to (src/render/canvas.h:76-89): "P6\n<W> <H>\n255\n" + W*H*3 bytes */
 int rtb_write_ppm(const char *path, int width, int height, const uint8_t *rgb8);

@@ -279,12 +279,16 @@ double ref_render(void *h, uint8_t *rgb, int threads, int quiet) {
 // calling the reference's Camera::cast_in_pixel and Scene::intersect), with
 //   * rng::normDist.reset() at the start of every pixel (per-pixel normal-distribution state),
 //   * pixel 0 seeded with `pixel0_seed` instead of std::random_device,
-// and the resolve of src/core/scene.cpp:54-63.  Work is split over `nproc` forked processes (row-interleaved)
-// because normDist is a single file-static object.  accum (W*H*3 floats, pre-resolve sums) may be null.
-double ref_render_deterministic(void *h, unsigned pixel0_seed, int nproc, float *accum, uint8_t *rgb) {
+// and the resolve of src/core/scene.cpp:54-63.  Work is split over `nproc` forked processes (pixel-interleaved)
+// because normDist is a single file-static object.  Rows [row_begin, row_end) only (a band of a BASELINE-sized frame is
+// what the parity tests can afford); accum ((row_end-row_begin)*W*3 floats, pre-resolve sums) may be null.
+double ref_render_deterministic_rows(void *h, unsigned pixel0_seed, int nproc, int row_begin, int row_end, float *accum, uint8_t *rgb) {
     Scene *s = (Scene *) h;
     const int W = s->camera->canvas.width(), H = s->camera->canvas.height();
-    const size_t bytes = (size_t) W * H * 3 * sizeof(float);
+    if (row_begin < 0 || row_end > H || row_begin > row_end) return -1.0;
+    const size_t npix = (size_t) W * (size_t) (row_end - row_begin);
+    if (npix == 0) return 0.0;
+    const size_t bytes = npix * 3 * sizeof(float);
     float *shared = (float *) mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_SHARED | MAP_ANONYMOUS, -1, 0);
     if (shared == MAP_FAILED) return -1.0;
     if (nproc <= 0) nproc = (int) sysconf(_SC_NPROCESSORS_ONLN);
@@ -294,8 +298,11 @@ double ref_render_deterministic(void *h, unsigned pixel0_seed, int nproc, float 
         pid_t pid = fork();
         if (pid == 0) {
             uniform_float_d offset(-0.5f, 0.5f);
-            for (int j = p; j < H; j += nproc) {
-                for (int i = 0; i < W; ++i) {
+            // pixels are independent (own engine, own normal-distribution state): deal them out in runs of 8 so that a
+            // band of a few rows still keeps every process busy
+            for (size_t q = (size_t) p * 8; q < npix; q += (size_t) nproc * 8) {
+                for (size_t idx = q; idx < q + 8 && idx < npix; ++idx) {
+                    const int j = row_begin + (int) (idx / (size_t) W), i = (int) (idx % (size_t) W);
                     rng::normDist.reset();
                     size_t seed = (size_t) j * W + i;
                     Engine e(seed != 0 ? (unsigned) seed : pixel0_seed);
@@ -307,7 +314,7 @@ double ref_render_deterministic(void *h, unsigned pixel0_seed, int nproc, float 
                         auto inter = s->intersect(r, e);
                         sum += inter.color;
                     }
-                    float *o = shared + ((size_t) j * W + i) * 3;
+                    float *o = shared + idx * 3;
                     o[0] = sum.x; o[1] = sum.y; o[2] = sum.z;
                 }
             }
@@ -325,7 +332,7 @@ double ref_render_deterministic(void *h, unsigned pixel0_seed, int nproc, float 
     if (accum) std::memcpy(accum, shared, bytes);
     if (rgb) {
         const float normalizer = 1.f / (float) s->samples;
-        for (size_t i = 0; i < (size_t) W * H; ++i) {
+        for (size_t i = 0; i < npix; ++i) {
             vector3f color{shared[i * 3], shared[i * 3 + 1], shared[i * 3 + 2]};
             color *= normalizer;
             color = aces_tonemap(color);
@@ -336,6 +343,10 @@ double ref_render_deterministic(void *h, unsigned pixel0_seed, int nproc, float 
     }
     munmap(shared, bytes);
     return bad ? -1.0 : sec;
+}
+double ref_render_deterministic(void *h, unsigned pixel0_seed, int nproc, float *accum, uint8_t *rgb) {
+    Scene *s = (Scene *) h;
+    return ref_render_deterministic_rows(h, pixel0_seed, nproc, 0, s->camera->canvas.height(), accum, rgb);
 }
 
 // One path through the reference's Scene::intersect for an explicit ray and engine state, with a fresh

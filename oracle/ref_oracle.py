@@ -46,6 +46,8 @@ def lib():
         L.ref_render.argtypes = [vp, vp, i32, i32]
         L.ref_render_deterministic.restype = f64
         L.ref_render_deterministic.argtypes = [vp, C.c_uint, i32, vp, vp]
+        L.ref_render_deterministic_rows.restype = f64
+        L.ref_render_deterministic_rows.argtypes = [vp, C.c_uint, i32, i32, i32, vp, vp]
         L.ref_trace_path.argtypes = [vp, vp, vp, C.c_uint, vp, vp]
         L.ref_minstd_first.restype = C.c_uint
         L.ref_minstd_first.argtypes = [C.c_uint]
@@ -170,12 +172,14 @@ class RefScene:
         sec = lib().ref_render(self.h, _p(rgb), threads, int(quiet))
         return rgb, sec
 
-    def render_deterministic(self, pixel0_seed=1, nproc=0):
+    def render_deterministic(self, pixel0_seed=1, nproc=0, rows=None):
+        """rows=(r0, r1): only that band of the frame (the outputs then hold r1 - r0 rows)"""
         cam = self.camera()
         H, W = int(cam["size"][1]), int(cam["size"][0])
-        rgb = np.zeros((H, W, 3), np.uint8)
-        acc = np.zeros((H, W, 3), np.float32)
-        sec = lib().ref_render_deterministic(self.h, pixel0_seed, nproc, _p(acc), _p(rgb))
+        r0, r1 = rows if rows is not None else (0, H)
+        rgb = np.zeros((r1 - r0, W, 3), np.uint8)
+        acc = np.zeros((r1 - r0, W, 3), np.float32)
+        sec = lib().ref_render_deterministic_rows(self.h, pixel0_seed, nproc, r0, r1, _p(acc), _p(rgb))
         if sec < 0:
             raise RuntimeError("ref_render_deterministic failed")
         return rgb, acc, sec

@@ -29,8 +29,12 @@ ABI_SYMBOLS = [
     "rtb_render", "rtb_render_device", "rtb_resolve_device", "rtb_render_local_rows", "rtb_render_global_row",
     "rtb_render_resume", "rtb_render_resume_device", "rtb_render_state_bytes", "rtb_scene_set_progress",
     "rtb_release_cached_memory",
+    "rtb_comm_unique_id", "rtb_comm_create", "rtb_comm_destroy", "rtb_comm_world", "rtb_comm_rank", "rtb_dist_rank_params",
+    "rtb_render_dist_device", "rtb_render_dist", "rtb_render_multi",
     "rtb_write_ppm",
 ]
+SPLIT_TILE, SPLIT_SAMPLE = 0, 1
+UNIQUE_ID_BYTES = 128
 
 
 class TextureDesc(C.Structure):
@@ -54,7 +58,8 @@ class SceneDesc(C.Structure):
 class RenderParams(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("samples", C.c_int32), ("row_begin", C.c_int32),
                 ("row_end", C.c_int32), ("pixel0_seed", C.c_uint32), ("sample_begin", C.c_int32), ("flags", C.c_int32),
-                ("interleave_count", C.c_int32), ("interleave_index", C.c_int32), ("interleave_rows", C.c_int32)]
+                ("interleave_count", C.c_int32), ("interleave_index", C.c_int32), ("interleave_rows", C.c_int32),
+                ("substreams", C.c_int32), ("substream_begin", C.c_int32), ("substream_end", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -122,6 +127,16 @@ def lib():
         L.rtb_scene_set_progress.argtypes = [C.c_void_p, PROGRESS_FN, C.c_void_p]
         L.rtb_resolve_device.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p]
         L.rtb_write_ppm.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p]
+        L.rtb_comm_unique_id.argtypes = [C.c_void_p]
+        L.rtb_comm_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.rtb_comm_destroy.argtypes = [C.c_void_p]
+        L.rtb_comm_destroy.restype = None
+        L.rtb_comm_world.argtypes = [C.c_void_p]
+        L.rtb_comm_rank.argtypes = [C.c_void_p]
+        L.rtb_dist_rank_params.argtypes = [C.POINTER(RenderParams), C.c_int, C.c_int, C.c_int, C.POINTER(RenderParams)]
+        L.rtb_render_dist_device.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(RenderParams), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.rtb_render_dist.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(RenderParams), C.c_int, C.c_void_p, C.POINTER(Stats)]
+        L.rtb_render_multi.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.POINTER(RenderParams), C.c_int, C.c_void_p, C.POINTER(Stats)]
         _lib = L
     return _lib
 
@@ -278,10 +293,19 @@ class Scene:
 
     def closest_hit(self, rays, cull=CULL_GLOBAL, counters=False, out=None):
         """rays: (n,6) float32 host array (numpy or pinned torch).  Returns dict(id,t,u,v,inside,stats)."""
+        if isinstance(rays, np.ndarray):
+            rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        else:   # a (pinned) torch tensor: must already be packed float32
+            assert str(rays.dtype) == "torch.float32" and rays.is_contiguous() and rays.shape[-1] == 6, "rays: contiguous float32 (n, 6)"
         n = rays.shape[0]
         if out is None:
             out = dict(id=np.empty(n, np.int32), t=np.empty(n, np.float32), u=np.empty(n, np.float32),
                        v=np.empty(n, np.float32), inside=np.empty(n, np.uint8))
+        else:
+            for key, dt in (("id", np.int32), ("t", np.float32), ("u", np.float32), ("v", np.float32), ("inside", np.uint8)):
+                a = out.get(key)
+                if isinstance(a, np.ndarray):
+                    assert a.dtype == dt and a.flags["C_CONTIGUOUS"] and a.size >= n, "out[%r]: contiguous %s of >= n elements" % (key, np.dtype(dt).name)
         st = Stats()
         if counters:
             st.box_tests = REQUEST_COUNTERS
@@ -302,12 +326,19 @@ class Scene:
         return out
 
     def render(self, width, height, samples, rows=None, pixel0_seed=1, counters=False, want_accum=True, want_rgb=True,
-               accum=None, rgb=None, reference_cull=False, megakernel=False, params=None):
-        """Replaces Scene::render.  HOST output buffers (numpy or pinned torch); copies are inside the call."""
+               accum=None, rgb=None, reference_cull=False, megakernel=False, params=None, substreams=0, substream_range=None):
+        """Replaces Scene::render.  HOST output buffers (numpy or pinned torch); copies are inside the call.
+        substreams = K > 1: the sample-range split (K engine streams per pixel); substream_range=(k0, k1) renders only
+        those streams and returns their partial sums (no rgb)."""
         if params is None:
             r0, r1 = rows if rows is not None else (0, height)
             flags = (1 if counters else 0) | (2 if reference_cull else 0) | (4 if megakernel else 0)
             params = RenderParams(width, height, samples, r0, r1, pixel0_seed, 0, flags)
+            params.substreams = substreams
+            if substream_range is not None:
+                params.substream_begin, params.substream_end = substream_range
+                if tuple(substream_range) != (0, max(1, substreams)):
+                    want_rgb = False
         n = lib().rtb_render_local_rows(C.byref(params))
         if n < 0:
             raise RtbError(RTB_ERR_INVALID, "bad render parameters")
@@ -350,6 +381,70 @@ class Scene:
     def render_device(self, params, d_accum=None, d_rgb8=None, d_counters=None, stream=0):
         """DEVICE output pointers (e.g. torch tensors), asynchronous on `stream` (a cudaStream_t handle)."""
         _check(lib().rtb_render_device(self.h, C.byref(params), _ptr(d_accum), _ptr(d_rgb8), _ptr(d_counters), C.c_void_p(stream)))
+
+
+def frame_params(width, height, samples, pixel0_seed=1, flags=0, substreams=0, interleave_rows=8):
+    """rtb_render_params of a WHOLE frame, as rtb_render_dist / rtb_render_multi take it"""
+    p = RenderParams(width, height, samples, 0, height, pixel0_seed, 0, flags, 0, 0, interleave_rows)
+    p.substreams = substreams
+    return p
+
+
+def rank_params(frame, split, world, rank):
+    """what rank `rank` of `world` renders for `frame` (rtb_dist_rank_params)"""
+    out = RenderParams()
+    _check(lib().rtb_dist_rank_params(C.byref(frame), split, world, rank, C.byref(out)))
+    return out
+
+
+def unique_id():
+    """rank 0: the bytes every rank hands to Comm (rtb_comm_unique_id = ncclGetUniqueId)"""
+    buf = (C.c_char * UNIQUE_ID_BYTES)()
+    _check(lib().rtb_comm_unique_id(buf))
+    return bytes(buf)
+
+
+class Comm:
+    """One rank's communicator (rtb_comm): NCCL over NVLink, one rank per GPU.  Collective constructor."""
+
+    def __init__(self, uid, world, rank, device):
+        h = C.c_void_p()
+        self._uid = C.create_string_buffer(uid, UNIQUE_ID_BYTES) if uid is not None else None
+        _check(lib().rtb_comm_create(self._uid, world, rank, device, C.byref(h)))
+        self.h, self.world, self.rank = h, world, rank
+
+    def close(self):
+        if self.h:
+            lib().rtb_comm_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def render_dist_device(scene, comm, frame, split, d_accum_root=None, d_rgb8_root=None, d_counters=None, stream=0):
+    """every rank calls; rank 0's device buffers receive the whole frame (rtb_render_dist_device)"""
+    _check(lib().rtb_render_dist_device(scene.h, comm.h if comm is not None else None, C.byref(frame), split, _ptr(d_accum_root),
+                                        _ptr(d_rgb8_root), _ptr(d_counters), C.c_void_p(stream)))
+
+
+def render_dist(scene, comm, frame, split, rgb_root=None):
+    """same with a HOST image on rank 0; returns this rank's stats"""
+    st = Stats()
+    _check(lib().rtb_render_dist(scene.h, comm.h if comm is not None else None, C.byref(frame), split, _ptr(rgb_root), C.byref(st)))
+    return st.as_dict()
+
+
+def render_multi(scenes, frame, split):
+    """one process, one thread per device (what the CLI runs): returns (H x W x 3 uint8 image, summed stats)"""
+    arr = (C.c_void_p * len(scenes))(*[s.h for s in scenes])
+    rgb = np.empty((frame.height, frame.width, 3), np.uint8)
+    st = Stats()
+    _check(lib().rtb_render_multi(arr, len(scenes), C.byref(frame), split, _ptr(rgb), C.byref(st)))
+    return rgb, st.as_dict()
 
 
 def release_cached_memory():

@@ -128,6 +128,9 @@ struct rtb_scene {
     // path state of the wavefront integrator (rtb_wavefront.cuh), grown on demand
     void *wf_state = nullptr;
     size_t wf_bytes = 0;
+    // buffers of the multi-GPU combine (rtb_dist.cu: local partial output, root staging), grown on demand
+    void *scratch[3] = {nullptr, nullptr, nullptr};
+    size_t scratch_bytes[3] = {0, 0, 0};
     unsigned long long launches = 0;   // kernels launched by rtb_render_device calls on this scene
     rtb::WfStreams wf_streams;               // slot-group streams of the wavefront integrator
     bool wf_streams_ok = false;
@@ -139,6 +142,7 @@ struct rtb_scene {
         for (auto &a : allocs) rtb::g_blocks.release(device, a.first, a.second);
         rtb::g_blocks.release(device, stage, stage_bytes);
         rtb::g_blocks.release(device, wf_state, wf_bytes);
+        for (int k = 0; k < 3; ++k) rtb::g_blocks.release(device, scratch[k], scratch_bytes[k]);
         for (auto &e : stage_events) cudaEventDestroy(e);
         if (wf_streams.graph_exec) cudaGraphExecDestroy(wf_streams.graph_exec);
         if (wf_streams.graph) cudaGraphDestroy(wf_streams.graph);
@@ -262,6 +266,23 @@ int ensure_stage(rtb_scene *sc, size_t bytes) {
 }
 
 }  // namespace
+
+namespace rtb {
+// device scratch block `which` (0..2) of a scene, at least `bytes` long (rtb_dist.cu)
+int scene_scratch(rtb_scene *sc, int which, size_t bytes, void **out) {
+    if (sc->scratch_bytes[which] < bytes) {
+        if (sc->scratch[which]) { RTB_CUDA(cudaDeviceSynchronize()); g_blocks.release(sc->device, sc->scratch[which], sc->scratch_bytes[which]); }
+        sc->scratch[which] = nullptr;
+        sc->scratch_bytes[which] = 0;
+        size_t got = 0;
+        RTB_CUDA(g_blocks.acquire(sc->device, bytes, &sc->scratch[which], &got));
+        sc->scratch_bytes[which] = got;
+    }
+    *out = sc->scratch[which];
+    return RTB_OK;
+}
+cudaStream_t scene_stream(rtb_scene *sc) { return sc->streams[0]; }
+}  // namespace rtb
 
 extern "C" {
 
@@ -482,11 +503,38 @@ int rtb_render_resume_device(rtb_scene *scene, const rtb_render_params *p, void 
     L.cull_mode = (p->flags & RTB_RENDER_REFERENCE_CULL) ? RTB_CULL_REFERENCE : RTB_CULL_GLOBAL;
     L.sample_begin = p->sample_begin;
     L.d_pixel_state = (uint4 *) d_pixel_state;
+    L.substreams = std::max(1, p->substreams);
+    L.sub_begin = 0;
+    L.sub_end = L.substreams;
+    L.plane_slots = 0;
+    if (L.substreams > 1) {
+        if (p->substream_begin != 0 || p->substream_end != 0) { L.sub_begin = p->substream_begin; L.sub_end = p->substream_end; }
+        if (L.sub_begin < 0 || L.sub_begin >= L.sub_end || L.sub_end > L.substreams) {
+            rtb::set_error("rtb_render_device: substream range outside [0, substreams)");
+            return RTB_ERR_INVALID;
+        }
+        if (d_pixel_state || p->sample_begin > 0 || (p->flags & (RTB_RENDER_REFERENCE_CULL | RTB_RENDER_MEGAKERNEL))) {
+            rtb::set_error("rtb_render_device: substreams > 1 runs on the wavefront integrator only and cannot be resumed");
+            return RTB_ERR_INVALID;
+        }
+        if (d_rgb8 && L.sub_end - L.sub_begin != L.substreams) {
+            rtb::set_error("rtb_render_device: a call that holds only part of a pixel's streams returns partial sums; rgb8 must be NULL");
+            return RTB_ERR_INVALID;
+        }
+        if ((unsigned long long) L.substreams * (unsigned long long) p->width * (unsigned long long) p->height >= 2147483646ull) {
+            rtb::set_error("rtb_render_device: substreams x width x height must stay below the engine's modulus");
+            return RTB_ERR_INVALID;
+        }
+    }
     // Integrator: the wavefront (ray-queue) form unless the caller asks for the megakernel; RTB_CULL_REFERENCE only
     // exists as a megakernel (the queue traverses with global-best culling).
     const bool mega = (p->flags & (RTB_RENDER_REFERENCE_CULL | RTB_RENDER_MEGAKERNEL)) != 0 || scene->d.ray_depth < 1 || scene->d.ray_depth > 15;
     if (mega && d_pixel_state) {
         rtb::set_error("rtb_render_resume: the pixel state is kept by the wavefront integrator only (no RTB_RENDER_MEGAKERNEL / RTB_RENDER_REFERENCE_CULL)");
+        return RTB_ERR_INVALID;
+    }
+    if (mega && L.substreams > 1) {
+        rtb::set_error("rtb_render_device: substreams > 1 needs ray_depth in [1, 15] (wavefront integrator)");
         return RTB_ERR_INVALID;
     }
     if (mega || local_rows == 0) {

@@ -34,10 +34,15 @@ struct RenderLaunch {
     // (src/core/scene.cpp:34-42), so this is everything a later call needs to carry on bit for bit.
     int sample_begin;
     uint4 *d_pixel_state;
+    // sample-range split (rtb_render_params::substreams): this launch runs streams [sub_begin, sub_end) of K = substreams
+    // per pixel; a stream is a slot, slot = (stream - sub_begin) * plane_slots + the pixel's slot in its 8x4 tile
+    int substreams, sub_begin, sub_end;
+    unsigned plane_slots;               // slots of one stream plane (tiles x 32); set by wf_slots()
 };
 void launch_render(const DScene &sc, const RenderLaunch &p, cudaStream_t stream);
 // wavefront (ray-queue) integrator, rtb_wavefront.cu; `state` = wf_alloc_bytes() bytes of device memory
-unsigned wf_slots(const RenderLaunch &p);
+unsigned wf_plane_slots(const RenderLaunch &p);   // slots of one stream plane
+unsigned wf_slots(const RenderLaunch &p);         // all planes of the launch
 size_t wf_alloc_bytes(unsigned n_slots, int depth_cap, int bvh_depth);
 // stage_events (may be null): filled with events bracketing every k_wf_trace launch, see rtb_scene_stage_ms()
 constexpr int kWfMaxGroups = 16;

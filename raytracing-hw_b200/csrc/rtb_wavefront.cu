@@ -123,6 +123,13 @@ __global__ void __launch_bounds__(kShadeBlock, MINB) k_wf_shade(const __grid_con
     }
 }
 
+// sample-range split: one thread per local pixel folds the pixel's streams in order (wf_fold_pixel)
+__global__ void __launch_bounds__(256) k_wf_fold(const RenderLaunch p, const WfState w) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t) p.local_rows * (size_t) p.width) return;
+    wf_fold_pixel(p, w, (int) (i % (size_t) p.width), (int) (i / (size_t) p.width));
+}
+
 // ---- order-preserving compaction: count per block, scan the block counts, scatter
 __global__ void __launch_bounds__(kCompactBlock) k_wf_count(const unsigned *__restrict__ list, const unsigned *__restrict__ n_list,
                                                             unsigned *__restrict__ block_counts) {
@@ -241,10 +248,11 @@ size_t wf_alloc_bytes(unsigned n_slots, int depth_cap, int bvh_depth) {
     return wf_state_bytes(n_slots, depth_cap, bvh_depth) + 13 * 256;
 }
 
-unsigned wf_slots(const RenderLaunch &p) {
+unsigned wf_plane_slots(const RenderLaunch &p) {
     const long long tiles = (long long) ((p.width + kWfTileW - 1) / kWfTileW) * ((p.local_rows + kWfTileH - 1) / kWfTileH);
     return (unsigned) (tiles * 32);
 }
+unsigned wf_slots(const RenderLaunch &p) { return wf_plane_slots(p) * (unsigned) std::max(1, p.substreams > 1 ? p.sub_end - p.sub_begin : 1); }
 
 // Measured on one B200 (Sponza stand-in, 64 spp, tail suspension on; profiles/r01k_groups_canvas_sweep.txt), Mpix*spp/s:
 //   1/2 of a 1080p frame (1.04 M slots): 268 / 258 / 234 with 1 / 2 / 4 groups
@@ -274,9 +282,12 @@ int wf_groups(unsigned n_slots, bool light_scene) {
 // independent, so the tail of one group's queue kernel (lanes running dry one by one) and its latency-bound shade
 // kernel overlap the other group's ALU-bound queue kernel.  With stage timing on, one group on the caller's stream:
 // a kernel's duration is only defined when it runs alone.
-void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *state, cudaStream_t stream, unsigned long long *launches,
+void launch_render_wavefront(const DScene &sc, const RenderLaunch &p_in, void *state, cudaStream_t stream, unsigned long long *launches,
                              std::vector<cudaEvent_t> *stage_events, WfStreams *aux) {
-    if (p.local_rows <= 0 || p.width <= 0 || p.samples <= 0) return;
+    if (p_in.local_rows <= 0 || p_in.width <= 0 || p_in.samples <= 0) return;
+    RenderLaunch p = p_in;
+    if (p.substreams <= 1) { p.substreams = 1; p.sub_begin = 0; p.sub_end = 1; }
+    p.plane_slots = wf_plane_slots(p);
     const unsigned n_slots = wf_slots(p);
     const int depth_cap = std::max(1, sc.ray_depth - 1);
     WfState w;
@@ -360,7 +371,9 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
     // samples x ray_depth iterations trace every ray a pixel can need when no ray is ever suspended; with suspension a
     // slot sometimes spends an iteration without finishing its ray, so a margin is enqueued up front and the live counts
     // are then read back (the one host synchronisation of a frame) until every group's list is empty
-    const long long base_iterations = (long long) (p.samples - p.sample_begin) * sc.ray_depth;
+    // (with K streams per pixel the longest stream has ceil(samples / K) samples)
+    const long long chain_samples = p.substreams > 1 ? ((long long) p.samples + p.substreams - 1) / p.substreams : (long long) (p.samples - p.sample_begin);
+    const long long base_iterations = chain_samples * sc.ray_depth;
     const long long iterations = tail_steps > 0 ? base_iterations + base_iterations / 16 + 8 : base_iterations;
     const int period = 16;   // iterations between compactions
     // optional stage timing: events[2*it], events[2*it+1] bracket iteration it's k_wf_trace; events[2*iterations] ends the frame
@@ -525,6 +538,11 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *stat
     }
     mark();
     join();
+    if (p.substreams > 1) {   // every stream of every pixel has finished: fold them into the pixels' sums
+        const size_t npix = (size_t) p.local_rows * (size_t) p.width;
+        k_wf_fold<<<(unsigned) ((npix + 255) / 256), 256, 0, stream>>>(p, w);
+        ++nl;
+    }
     if (progress) {   // (with a progress line the call returns when the frame is complete)
         cudaStreamSynchronize(stream);
         prog_call(100);

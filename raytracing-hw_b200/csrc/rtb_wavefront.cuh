@@ -42,6 +42,7 @@ struct WfState {
 
 RTB_HD bool wf_slot_pixel(const RenderLaunch &p, unsigned slot, int &px, int &lr, int &py) {
     const int tiles_x = (p.width + kWfTileW - 1) / kWfTileW;
+    if (slot >= p.plane_slots) slot %= p.plane_slots;   // (stream planes beyond the first: same pixel layout)
     const unsigned tile = slot >> 5, lane = slot & 31u;
     const int tx = (int) (tile % (unsigned) tiles_x), ty = (int) (tile / (unsigned) tiles_x);
     px = tx * kWfTileW + (int) (lane & (kWfTileW - 1));
@@ -49,6 +50,25 @@ RTB_HD bool wf_slot_pixel(const RenderLaunch &p, unsigned slot, int &px, int &lr
     py = p.row_begin + lr;
     if (p.il_count > 1) py = p.row_begin + ((lr / p.il_rows) * p.il_count + p.il_index) * p.il_rows + lr % p.il_rows;
     return px < p.width && lr < p.local_rows && py < p.row_end;
+}
+
+// sample range [s0, s1) of the stream a slot runs (rtb_render_params::substreams; one stream: [sample_begin, samples))
+RTB_HD void wf_slot_samples(const RenderLaunch &p, unsigned slot, int &stream, int &s0, int &s1) {
+    if (p.substreams <= 1) {
+        stream = 0;
+        s0 = p.sample_begin;
+        s1 = p.samples;
+        return;
+    }
+    stream = p.sub_begin + (int) (slot / p.plane_slots);
+    s0 = (int) ((long long) stream * p.samples / p.substreams);
+    s1 = (int) ((long long) (stream + 1) * p.samples / p.substreams);
+}
+// slot of pixel (px, local row lr) in stream plane `plane` of the launch
+RTB_HD unsigned wf_pixel_slot(const RenderLaunch &p, int px, int lr, int plane) {
+    const int tiles_x = (p.width + kWfTileW - 1) / kWfTileW;
+    const unsigned tile = (unsigned) (lr / kWfTileH) * (unsigned) tiles_x + (unsigned) (px / kWfTileW);
+    return (unsigned) plane * p.plane_slots + tile * 32u + (unsigned) ((lr % kWfTileH) * kWfTileW + px % kWfTileW);
 }
 
 RTB_HD void wf_store_ray(const WfState &w, unsigned slot, V3 o, V3 d) {
@@ -68,6 +88,12 @@ RTB_HD unsigned wf_init_slot(const DScene &sc, const RenderLaunch &p, const WfSt
     if (!wf_slot_pixel(p, slot, px, lr, py)) return slot | kSlotDone;
     Rng g;
     float4 sum0 = make_float4(0.f, 0.f, 0.f, 0.f);
+    int stream, s0, s1;
+    wf_slot_samples(p, slot, stream, s0, s1);
+    if (s0 >= s1) {   // more streams than samples: this one has none (its sum is zero)
+        w.sum[slot] = sum0;
+        return slot | kSlotDone;
+    }
     if (p.sample_begin > 0) {   // resume: the pixel's engine and sum as an earlier call left them
         const size_t o = ((size_t) lr * p.width + px) * 2;
         const uint4 a = p.d_pixel_state[o], b = p.d_pixel_state[o + 1];
@@ -76,7 +102,8 @@ RTB_HD unsigned wf_init_slot(const DScene &sc, const RenderLaunch &p, const WfSt
         g.has_saved = (a.z & 1u) != 0u;
         sum0 = make_float4(u2f(b.x), u2f(b.y), u2f(b.z), 0.f);
     } else {
-        const uint64_t seed = (uint64_t) py * (uint64_t) p.width + (uint64_t) px;
+        // stream k of a pixel is seeded like the pixel k canvases further down (stream 0: the reference's own seed)
+        const uint64_t seed = (uint64_t) stream * (uint64_t) p.width * (uint64_t) p.height + (uint64_t) py * (uint64_t) p.width + (uint64_t) px;
         rng_seed(g, seed != 0 ? seed : (uint64_t) p.pixel0_seed);
     }
     const float ox = rng_pixel_offset(g);
@@ -84,7 +111,7 @@ RTB_HD unsigned wf_init_slot(const DScene &sc, const RenderLaunch &p, const WfSt
     // Camera::cast_in_pixel hands the un-normalised direction to Ray::Ray; store exactly that
     const V3 d = camera_dir(sc, px, py, p.width, p.height, ox, oy);
     wf_store_ray(w, slot, V3{sc.cam_pos[0], sc.cam_pos[1], sc.cam_pos[2]}, d);
-    w.ctl[slot] = make_uint4(g.x, f2u(g.saved), (unsigned) p.sample_begin, (g.has_saved ? 256u : 0u));
+    w.ctl[slot] = make_uint4(g.x, f2u(g.saved), (unsigned) s0, (g.has_saved ? 256u : 0u));
     w.sum[slot] = sum0;
     return slot;
 }
@@ -190,7 +217,13 @@ RTB_HD unsigned wf_shade_slot(const DScene &sc, const RenderLaunch &p, const WfS
         n = 0;
         int px, lr, py;
         wf_slot_pixel(p, slot, px, lr, py);
-        if (sample >= p.samples) {
+        int stream, s0, s1;
+        wf_slot_samples(p, slot, stream, s0, s1);
+        if (sample >= s1 && p.substreams > 1) {
+            // one of several streams of the pixel: its sum waits in the slot for wf_fold_pixel
+            w.sum[slot] = make_float4(sum.x, sum.y, sum.z, 0.f);
+            entry = slot | kSlotDone;
+        } else if (sample >= s1) {
             const size_t o = ((size_t) lr * p.width + px) * 3;
             if (p.d_accum) {
                 p.d_accum[o] = sum.x;
@@ -219,6 +252,31 @@ RTB_HD unsigned wf_shade_slot(const DScene &sc, const RenderLaunch &p, const WfS
     }
     w.ctl[slot] = make_uint4(g.x, f2u(g.saved), (unsigned) sample, (unsigned) k | ((unsigned) n << 4) | (g.has_saved ? 256u : 0u));
     return entry;
+}
+
+// Sample-range split: the sums of the launch's streams of pixel (px, local row lr), folded in stream order
+// (src/core/scene.cpp:42 accumulates a pixel's samples in order; here each stream's samples are in order and the streams
+// follow one another), written to d_accum and -- when the launch holds every stream of the pixel -- resolved to d_rgb8.
+RTB_HD void wf_fold_pixel(const RenderLaunch &p, const WfState &w, int px, int lr) {
+    const int planes = p.sub_end - p.sub_begin;
+    const float4 s = w.sum[wf_pixel_slot(p, px, lr, 0)];
+    V3 sum = V3{s.x, s.y, s.z};
+    for (int k = 1; k < planes; ++k) {
+        const float4 t = w.sum[wf_pixel_slot(p, px, lr, k)];
+        sum = sum + V3{t.x, t.y, t.z};
+    }
+    const size_t o = ((size_t) lr * p.width + px) * 3;
+    if (p.d_accum) {
+        p.d_accum[o] = sum.x;
+        p.d_accum[o + 1] = sum.y;
+        p.d_accum[o + 2] = sum.z;
+    }
+    if (p.d_rgb8) {
+        const float normalizer = 1.f / (float) p.samples;
+        p.d_rgb8[o] = resolve_channel(sum.x, normalizer);
+        p.d_rgb8[o + 1] = resolve_channel(sum.y, normalizer);
+        p.d_rgb8[o + 2] = resolve_channel(sum.z, normalizer);
+    }
 }
 
 // ---- launchers (rtb_wavefront.cu)

@@ -1,25 +1,28 @@
-"""Multi-GPU plumbing: one process per GPU (torch.distributed), rows of the canvas dealt out in interleaved blocks.
+"""Rank plumbing for one-process-per-GPU launches (torchrun) around librtb's own multi-GPU layer.
 
-The reference has no distributed mode (one OpenMP loop over pixels, src/core/scene.cpp:31).  The render shards
-trivially by pixel; rows are cut into blocks of `interleave_rows` rows and block b goes to rank b % world, so that
-(i) every pixel keeps its own sequential sample stream -- the image does not depend on the number of GPUs -- and
-(ii) expensive image regions are spread over all ranks.  There is no data-path collective: the only exchange is the
-end-of-frame gather of each rank's resolved rows (RGB8, or the fp32 sums) to rank 0 over NCCL/NVLink (gloo on CPU
-in the tests).  Nothing here computes pixels; it only builds rtb_render_params and moves finished rows."""
+The partition of the frame and the NCCL combine live in the product (csrc/rtb_dist.cu: rtb_comm_*, rtb_render_dist*);
+this module only (i) hands rank 0's NCCL unique id to the other ranks through torch.distributed and builds the rank's
+rtb.Comm, and (ii) mirrors the combine on HOST tensors over gloo for the CPU tests (tests/test_dist_cpu.py), where no
+GPU -- hence no NCCL -- exists.  Nothing here computes pixels.
+
+  tile split   : interleaved row blocks, block b on rank b % world; combine = gather of each rank's compact rows to
+                 rank 0, rows put in place (bit-identical to the one-GPU frame)
+  sample split : every rank renders the whole canvas with its share of the K engine streams per pixel; combine = sum
+                 reduction of the fp32 partial sums to rank 0"""
 import numpy as np
 import torch
 import torch.distributed as dist
 
-from . import RenderParams
-
-DEFAULT_INTERLEAVE_ROWS = 8
+from . import SPLIT_SAMPLE, SPLIT_TILE, Comm, frame_params, rank_params, unique_id   # noqa: F401
 
 
-def rank_params(width, height, samples, world, rank, pixel0_seed=1, flags=0, interleave_rows=DEFAULT_INTERLEAVE_ROWS):
-    """rtb_render_params of `rank`: all rows when world == 1, else the interleaved row blocks of that rank."""
+def make_comm(world, rank, device):
+    """Collective: this rank's rtb.Comm (None when world == 1).  torch.distributed must be initialised."""
     if world <= 1:
-        return RenderParams(width, height, samples, 0, height, pixel0_seed, 0, flags, 0, 0, 0)
-    return RenderParams(width, height, samples, 0, height, pixel0_seed, 0, flags, world, rank, interleave_rows)
+        return None
+    box = [unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    return Comm(box[0], world, rank, device)
 
 
 def local_rows(p):
@@ -31,22 +34,28 @@ def local_rows(p):
     return rows[blk % p.interleave_count == p.interleave_index]
 
 
-def gather_rows(local, width, height, samples, world, rank, group=None, interleave_rows=DEFAULT_INTERLEAVE_ROWS, dst=0):
-    """local: (local_rows, width, C) tensor on this rank's device (cuda with NCCL, cpu with gloo).  Returns the
-    (height, width, C) image on rank `dst` (None elsewhere).  One all_gather of equally padded blocks."""
+def combine_host(local, frame, split, world, rank, group=None, dst=0):
+    """The combine of rtb_render_dist on HOST tensors over the current (gloo) process group -- CPU tests only.
+    local: this rank's (rows, width, C) result for rank_params(frame, split, world, rank).  Returns the
+    (height, width, C) frame on rank `dst`, None elsewhere."""
     if world <= 1:
         return local
-    counts = [len(local_rows(rank_params(width, height, samples, world, r, interleave_rows=interleave_rows))) for r in range(world)]
-    pad = max(counts)
-    buf = torch.zeros((pad,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
-    buf[: local.shape[0]] = local
-    out = torch.empty((world * pad,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
-    dist.all_gather_into_tensor(out, buf, group=group)
-    if rank != dst:
-        return None
-    image = torch.empty((height,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
-    for r in range(world):
-        rows = torch.as_tensor(local_rows(rank_params(width, height, samples, world, r, interleave_rows=interleave_rows)),
-                               device=local.device, dtype=torch.long)
-        image[rows] = out[r * pad: r * pad + counts[r]]
-    return image
+    if split == SPLIT_SAMPLE:
+        total = local.clone()
+        dist.reduce(total, dst=dst, op=dist.ReduceOp.SUM, group=group)
+        return total if rank == dst else None
+    counts = [len(local_rows(rank_params(frame, split, world, r))) for r in range(world)]
+    parts = [torch.empty((c,) + tuple(local.shape[1:]), dtype=local.dtype) for c in counts] if rank == dst else None
+    # (gloo's gather wants equal shapes: send / recv the ragged blocks point to point, as the product does with NCCL)
+    if rank == dst:
+        parts[dst] = local
+        reqs = [dist.irecv(parts[r], src=r, group=group) for r in range(world) if r != dst and counts[r] > 0]
+        for q in reqs:
+            q.wait()
+        image = torch.empty((frame.height,) + tuple(local.shape[1:]), dtype=local.dtype)
+        for r in range(world):
+            image[torch.as_tensor(local_rows(rank_params(frame, split, world, r)), dtype=torch.long)] = parts[r]
+        return image
+    if counts[rank] > 0:
+        dist.send(local.contiguous(), dst=dst, group=group)
+    return None

@@ -160,9 +160,14 @@ def devsim_light_pdf(hs, rays):
     return out
 
 
-def devsim_render(hs, width, height, samples, rows=None, pixel0_seed=1, reference_cull=False, wavefront=False, interleave=None):
+def devsim_render(hs, width, height, samples, rows=None, pixel0_seed=1, reference_cull=False, wavefront=False, interleave=None,
+                  substreams=0, substream_range=None):
     r0, r1 = rows if rows is not None else (0, height)
     p = rtb.RenderParams(width, height, samples, r0, r1, pixel0_seed, 0, 2 if reference_cull else 0)
+    p.substreams = substreams
+    if substream_range is not None:
+        p.substream_begin, p.substream_end = substream_range
+    wavefront = wavefront or substreams > 1
     n_rows = r1 - r0
     if interleave is not None:
         p.interleave_count, p.interleave_index, p.interleave_rows = interleave

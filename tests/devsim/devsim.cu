@@ -225,7 +225,13 @@ int devsim_render_wavefront_resume(const rtb_scene_desc *desc, const rtb_render_
     L.sample_begin = p->sample_begin;
     L.d_pixel_state = (uint4 *) pixel_state;
     if (p->sample_begin > 0 && !pixel_state) { g_err = "sample_begin > 0 without a pixel state"; return 3; }
-    const unsigned n_slots = (unsigned) (((L.width + kWfTileW - 1) / kWfTileW) * ((L.local_rows + kWfTileH - 1) / kWfTileH) * 32);
+    // sample-range split (rtb_render_params::substreams), as rtb_render_resume_device sets it up
+    L.substreams = std::max(1, p->substreams);
+    L.sub_begin = 0; L.sub_end = L.substreams;
+    if (L.substreams > 1 && (p->substream_begin != 0 || p->substream_end != 0)) { L.sub_begin = p->substream_begin; L.sub_end = p->substream_end; }
+    if (L.sub_begin < 0 || L.sub_begin >= L.sub_end || L.sub_end > L.substreams) { g_err = "bad substream range"; return 3; }
+    L.plane_slots = (unsigned) (((L.width + kWfTileW - 1) / kWfTileW) * ((L.local_rows + kWfTileH - 1) / kWfTileH) * 32);
+    const unsigned n_slots = L.plane_slots * (unsigned) (L.sub_end - L.sub_begin);
     const int cap = std::max(1, s.d.ray_depth - 1);
     std::vector<float4> ray_a(n_slots), hit(n_slots), sum(n_slots), stk_e((size_t) n_slots * cap), stk_m((size_t) n_slots * cap);
     std::vector<float2> ray_b(n_slots);
@@ -238,7 +244,8 @@ int devsim_render_wavefront_resume(const rtb_scene_desc *desc, const rtb_render_
     std::vector<unsigned> list(n_slots);
     for (unsigned i = 0; i < n_slots; ++i) list[i] = wf_init_slot(s.d, L, w, i);
     unsigned long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;
-    const long long iterations = (long long) (p->samples - p->sample_begin) * s.d.ray_depth;
+    const long long chain = L.substreams > 1 ? ((long long) p->samples + L.substreams - 1) / L.substreams : (long long) (p->samples - p->sample_begin);
+    const long long iterations = chain * s.d.ray_depth;
     for (long long it = 0; it < iterations; ++it) {
 #pragma omp parallel for schedule(dynamic, 64) reduction(+ : c0, c1, c2, c3)
         for (long long i = 0; i < (long long) n_slots; ++i) {
@@ -259,6 +266,9 @@ int devsim_render_wavefront_resume(const rtb_scene_desc *desc, const rtb_render_
         int px, lr, py;
         if (wf_slot_pixel(L, i, px, lr, py) && !(list[i] & kSlotDone)) { g_err = "a slot did not finish"; return 2; }
     }
+    if (L.substreams > 1)
+        for (int lr = 0; lr < L.local_rows; ++lr)
+            for (int px = 0; px < L.width; ++px) wf_fold_pixel(L, w, px, lr);
     if (counters4) { counters4[0] = c0; counters4[1] = c1; counters4[2] = c2; counters4[3] = c3; }
     return 0;
 }

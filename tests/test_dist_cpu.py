@@ -1,6 +1,8 @@
-"""N>1 host logic on CPU: two processes (gloo), each "renders" its interleaved row blocks with the host-compiled
-device code (tests/devsim -- there is no GPU here), rows are gathered to rank 0 by raytracing-hw_b200/dist.py and the
-result must equal the single-process image bit for bit."""
+"""N>1 host logic on CPU: two processes (gloo), each "renders" its share of the frame -- the rtb_render_params librtb's
+rtb_dist_rank_params gives the rank, for both splits -- with the host-compiled device code (tests/devsim: there is no
+GPU here); the results are combined on rank 0 by raytracing-hw_b200/dist.py's host mirror of rtb_render_dist's combine
+and must equal the single-process frame bit for bit (tile split: the reference's streams; sample split: the same K
+streams per pixel, two partial sums added)."""
 import importlib
 import os
 import socket
@@ -22,7 +24,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, W, H, S, out_path):
+def _worker(rank, world, port, W, H, S, out_path, split=0, K=0):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     os.environ["OMP_NUM_THREADS"] = "2"
@@ -31,11 +33,13 @@ def _worker(rank, world, port, W, H, S, out_path):
     rdist = importlib.import_module("raytracing-hw_b200.dist")
     dist.init_process_group("gloo", rank=rank, world_size=world)
     hs = u.rtb.HostScene.load_gltf(u.scene_path("s7_4"), W, H, S)
-    p = rdist.rank_params(W, H, S, world, rank, interleave_rows=4)
-    rows = rdist.local_rows(p)
-    # devsim renders a contiguous row range; render each of this rank's blocks
-    local = np.concatenate([u.devsim_render(hs, W, H, S, rows=(int(r), int(r) + 1))["accum"] for r in rows])
-    img = rdist.gather_rows(torch.from_numpy(local), W, H, S, world, rank, interleave_rows=4)
+    frame = u.rtb.frame_params(W, H, S, substreams=K, interleave_rows=4)
+    p = rdist.rank_params(frame, split, world, rank)
+    if split == rdist.SPLIT_TILE:
+        local = u.devsim_render(hs, W, H, S, interleave=(p.interleave_count, p.interleave_index, p.interleave_rows), wavefront=True)["accum"]
+    else:
+        local = u.devsim_render(hs, W, H, S, substreams=p.substreams, substream_range=(p.substream_begin, p.substream_end))["accum"]
+    img = rdist.combine_host(torch.from_numpy(local), frame, split, world, rank)
     if rank == 0:
         np.save(out_path, img.numpy())
     else:
@@ -53,13 +57,46 @@ def test_two_rank_gather_equals_single_process(tmp_path):
     assert np.array_equal(np.load(out), full)
 
 
+def test_two_rank_sample_split_equals_single_process(tmp_path):
+    """sample split: rank r renders streams [r K / 2, (r + 1) K / 2) of every pixel; the reduced sums equal the
+    single-process K-stream frame when each rank holds ONE stream (a + b has one rounding), and stay within a few ulp
+    of it when a rank folds several streams first (the fold order differs: (a + b) + (c + d) vs ((a + b) + c) + d)"""
+    W, H, S = 24, 16, 6
+    hs = _util.rtb.HostScene.load_gltf(_util.scene_path("s7_4"), W, H, S)
+    out = str(tmp_path / "img2.npy")
+    mp.spawn(_worker, args=(2, _free_port(), W, H, S, out, 1, 0), nprocs=2, join=True)
+    full = _util.devsim_render(hs, W, H, S, substreams=2)["accum"]
+    assert np.array_equal(np.load(out), full)
+    out4 = str(tmp_path / "img4.npy")
+    mp.spawn(_worker, args=(2, _free_port(), W, H, S, out4, 1, 4), nprocs=2, join=True)
+    full4 = _util.devsim_render(hs, W, H, S, substreams=4)["accum"]
+    assert np.allclose(np.load(out4), full4, rtol=4e-7, atol=0)
+
+
+def test_rank_params_of_both_splits():
+    rtb = _util.rtb
+    f = rtb.frame_params(100, 1080, 1024, substreams=0)
+    for world in (1, 2, 3, 4, 8):
+        streams = []
+        for r in range(world):
+            q = rtb.rank_params(f, rtb.SPLIT_SAMPLE, world, r)
+            assert q.substreams == world and (q.row_begin, q.row_end, q.interleave_count) == (0, 1080, 0)
+            streams += list(range(q.substream_begin, q.substream_end))
+        assert streams == list(range(world))
+    f.substreams = 16
+    q = rtb.rank_params(f, rtb.SPLIT_SAMPLE, 8, 3)
+    assert (q.substreams, q.substream_begin, q.substream_end) == (16, 6, 8)
+    q = rtb.rank_params(f, rtb.SPLIT_TILE, 1, 0)
+    assert q.interleave_count == 0 and q.substreams == 16   # K streams per pixel on one GPU: allowed with the tile split
+
+
 def test_rank_rows_partition():
     rdist = importlib.import_module("raytracing-hw_b200.dist")
     import ctypes as C
     for world in (1, 2, 3, 4, 8):
         seen = []
         for r in range(world):
-            p = rdist.rank_params(100, 1080, 4, world, r)
+            p = rdist.rank_params(_util.rtb.frame_params(100, 1080, 4), rdist.SPLIT_TILE, world, r)
             rows = rdist.local_rows(p)
             n = _util.rtb.lib().rtb_render_local_rows(C.byref(p))
             assert n == len(rows)

@@ -97,7 +97,7 @@ def test_row_ranges_and_interleave_compose(host_scene):
     dist = __import__("importlib").import_module("raytracing-hw_b200.dist")
     image = np.zeros_like(full)
     for rank in range(3):
-        p = dist.rank_params(W, H, S, 3, rank, interleave_rows=4)
+        p = rtb.rank_params(rtb.frame_params(W, H, S, interleave_rows=4), rtb.SPLIT_TILE, 3, rank)
         image[dist.local_rows(p)] = sc.render(W, H, S, params=p)["accum"]
     assert np.array_equal(image, full)
     # empty row range
