@@ -6,8 +6,12 @@
 
 A "step" is one full render of the workload (BASELINE.json configs[3]: examples/sponza at 1920x1080, 1024 spp --
 on the stand-in scene of scenes/gen_scenes.py, because the reference's geometry buffer was never shipped, SURVEY.md
-0.3).  Rows are dealt to the ranks in interleaved blocks (raytracing-hw_b200/dist.py); the step ends with the NCCL
-gather of the finished RGB8 rows on rank 0.  Total work is fixed as N grows: "scaling": "strong".
+0.3), through librtb's own multi-GPU entry point rtb_render_dist_device (csrc/rtb_dist.cu): one rank per GPU, one NCCL
+combine per frame on rank 0.  --split sample (default for N > 1): every rank renders the whole canvas with its share
+of N engine streams per pixel, ncclReduce of the fp32 sums + resolve on rank 0 (statistically equivalent to the
+reference's stream, gated in tests/); --split tile: interleaved row blocks, every pixel keeps the reference's own
+stream (bit-identical frame), ncclSend/ncclRecv of the RGB8 rows.  N = 1 is always the bit-exact mode.  Total work is
+fixed as N grows: "scaling": "strong".
 
 value  : Mpix*spp/s of the whole job, scene resident in HBM, device-timed (CUDA events, max over ranks).
 e2e    : same metric through the C ABI with HOST buffers: rtb_scene_create (host->device copy of the whole scene) +
@@ -51,6 +55,10 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample", default="960x540x24", help="WxHxS of the bounded CPU sample (about 10-30 s of host work)")
     ap.add_argument("--megakernel", action="store_true", help="time the first integrator (one thread per pixel) instead of the ray queue")
+    ap.add_argument("--split", default="auto", choices=["auto", "tile", "sample"],
+                    help="multi-GPU partition (auto: sample for N > 1); see the module docstring")
+    ap.add_argument("--substreams", type=int, default=0, help="engine streams per pixel (0: one per rank with --split sample, else 1)")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (diagnostic sweeps)")
     return ap.parse_args()
 
 
@@ -190,25 +198,23 @@ def run_b200_arm(args):
     path = gen_scenes.ensure(scene)
     hs = rtb.HostScene.load_gltf(path, W, H, S)
     sc = rtb.Scene(hs, local)
-    params = rdist.rank_params(W, H, S, world, rank)
-    n_local = len(rdist.local_rows(params))
-    d_rgb = torch.empty((n_local, W, 3), dtype=torch.uint8, device="cuda")
+    split_name = args.split if args.split != "auto" else ("sample" if world > 1 else "tile")
+    split = rtb.SPLIT_SAMPLE if split_name == "sample" else rtb.SPLIT_TILE
+    flags = rtb.RENDER_MEGAKERNEL if args.megakernel else 0
+    frame = rtb.frame_params(W, H, S, pixel0_seed=1, flags=flags, substreams=args.substreams)
+    params = rtb.rank_params(frame, split, world, rank)           # what this rank renders (for the roofline leg)
+    comm = rdist.make_comm(world, rank, local)                    # rtb_comm over NCCL: the product's own communicator
+    d_rgb = torch.empty((H, W, 3), dtype=torch.uint8, device="cuda") if rank == 0 else None
     d_cnt = torch.zeros(6, dtype=torch.int64, device="cuda")
-    if args.megakernel:
-        params.flags |= rtb.RENDER_MEGAKERNEL
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
     stream = torch.cuda.current_stream().cuda_stream
-    image = [None]
 
     def step(ev=None):
         if ev:
             ev[0].record()
-        sc.render_device(params, d_accum=None, d_rgb8=d_rgb, d_counters=d_cnt, stream=stream)
+        rtb.render_dist_device(sc, comm, frame, split, d_rgb8_root=d_rgb, d_counters=d_cnt, stream=stream)
         if ev:
             ev[1].record()
-        image[0] = rdist.gather_rows(d_rgb, W, H, S, world, rank)
-        if ev:
-            ev[2].record()
 
     for _ in range(args.warmup):
         flush.zero_()
@@ -218,7 +224,7 @@ def run_b200_arm(args):
     sampler = ClockSampler(local)
     sampler.start()
     launches0 = sc.launches
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(args.steps)]
     barrier()
     t_wall = time.perf_counter()
     for k in range(args.steps):
@@ -228,105 +234,133 @@ def run_b200_arm(args):
     t_wall = time.perf_counter() - t_wall
     clocks = sampler.stop()
     launches = sc.launches - launches0
-    step_ms = sum(e[0].elapsed_time(e[2]) for e in evs)
-    kern_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
+    step_ms = sum(e[0].elapsed_time(e[1]) for e in evs)
     t = torch.tensor([step_ms], dtype=torch.float64, device="cuda")
     cnt = d_cnt.clone()
+    nl = torch.tensor([launches], dtype=torch.int64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+        dist.all_reduce(nl, op=dist.ReduceOp.SUM)
     ms_per_step = float(t[0]) / args.steps
     rays_per_step = int(cnt[0]) / args.steps
     lq_per_step = int(cnt[1]) / args.steps
     value = W * H * S / (ms_per_step * 1e-3) * 1e-6
 
-    # ---- e2e: host buffers through the C ABI; scene upload + render + image download inside the timed region
-    h_rgb = torch.empty((n_local, W, 3), dtype=torch.uint8).pin_memory()
+    # ---- e2e: host buffers through the C ABI; scene upload + render + combine + image download inside the timed region
     h_img = torch.empty((H, W, 3), dtype=torch.uint8).pin_memory() if rank == 0 else None
     upload_bytes = sc.upload_bytes
+    e2e_value = None
 
     def e2e_step():
         s2 = rtb.Scene(hs, local)                                   # H2D: nodes, triangles, shading records, textures
-        if world == 1:
-            s2.render(W, H, S, params=params, want_accum=False, rgb=h_rgb.numpy())      # D2H inside rtb_render
-        else:
-            s2.render_device(params, d_accum=None, d_rgb8=d_rgb, d_counters=None, stream=stream)
-            img = rdist.gather_rows(d_rgb, W, H, S, world, rank)
-            if rank == 0:
-                h_img.copy_(img, non_blocking=True)
-            torch.cuda.synchronize()
+        rtb.render_dist(s2, comm, frame, split, h_img.numpy() if rank == 0 else None)      # D2H of the frame inside the call
         s2.close()
 
-    e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    n_e2e = max(1, min(args.steps, 2))
-    for _ in range(n_e2e):
+    if not args.no_e2e:
         e2e_step()
-    barrier()
-    te = torch.tensor([(time.perf_counter() - t0) / n_e2e], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_value = W * H * S / float(te[0]) * 1e-6
+        barrier()
+        t0 = time.perf_counter()
+        n_e2e = max(1, min(args.steps, 2))
+        for _ in range(n_e2e):
+            e2e_step()
+        barrier()
+        te = torch.tensor([(time.perf_counter() - t0) / n_e2e], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e_value = W * H * S / float(te[0]) * 1e-6
+    K = max(1, params.substreams)
+    if split == rtb.SPLIT_SAMPLE:
+        par = ("sample-range split: %d engine stream(s) per pixel, %d per rank, whole canvas on each of %d rank(s); ncclReduce(sum) of the fp32 sums "
+               "+ resolve on rank 0 (rtb_render_dist)" % (K, max(1, params.substream_end - params.substream_begin) if K > 1 else 1, world))
+    else:
+        par = "tile split: row blocks of 8 interleaved over %d rank(s), the reference's own stream per pixel%s; ncclSend/ncclRecv of RGB8 rows to rank 0 (rtb_render_dist)" % (
+            world, "" if K <= 1 else " x %d streams" % K)
     return dict(rtb=rtb, sc=sc, hs=hs, path=path, rank=rank, world=world, W=W, H=H, S=S, name=name, value=value,
-                ms_per_step=ms_per_step, kern_ms=kern_ms, rays_per_step=rays_per_step, lq_per_step=lq_per_step,
-                clocks=clocks, e2e_value=e2e_value, upload_bytes=upload_bytes, t_wall=t_wall, params=params,
-                n_local=n_local, torch=torch, dist=dist, launches=launches, d_rgb=d_rgb, stream=stream, megakernel=args.megakernel)
+                ms_per_step=ms_per_step, rays_per_step=rays_per_step, lq_per_step=lq_per_step, scene=scene,
+                clocks=clocks, e2e_value=e2e_value, upload_bytes=upload_bytes, t_wall=t_wall, params=params, frame=frame,
+                torch=torch, dist=dist, launches=int(nl[0]), stream=stream, megakernel=args.megakernel, parallelism=par, comm=comm)
 
 
 def roofline(r):
     """Dominant kernel: k_wf_trace, the closest-hit queue (k_render with --megakernel).  Algorithmic bytes = 28 B per
     ray/box test + 36 B per ray/triangle test performed by the shipped traversal order on the scene BVH,
-    counted by the counting instantiation of the same kernels at a reduced spp on the same rows and scaled by the
+    counted by the counting instantiation of the same kernels at a reduced spp on this rank's pixels and scaled by the
     sample ratio (tests per sample are spp-independent).  Kernel time: CUDA events recorded on the launching stream
-    around every queue launch of one extra frame (RTB_RENDER_STAGE_TIMES); `achieved` = all queue launches' bytes /
-    all queue launches' time = bytes per launch / average launch duration."""
-    rtb, sc, p = r["rtb"], r["sc"], r["params"]
-    spp_c = min(r["S"], 4)
-    pc = rtb.RenderParams(p.width, p.height, spp_c, p.row_begin, p.row_end, p.pixel0_seed, 0, 1 | (p.flags & rtb.RENDER_MEGAKERNEL),
+    around every queue launch of one extra frame of this rank's share (RTB_RENDER_STAGE_TIMES); `achieved` = all queue
+    launches' bytes / all queue launches' time = bytes per launch / average launch duration.
+    Denominator (two regimes): a traversal set that fits the L2 is up against the L2 -- `peak` = the rate
+    at which this GPU gathers 64-byte records at random indices from an L2-resident buffer (rtb_measure_l2, measured in
+    this run; the streaming rate is reported beside it); one that does not is up against HBM -- `peak` =
+    MEASURED_PEAKS.json hbm_gbs.  frac_hbm is always reported."""
+    rtb, sc, p, torch = r["rtb"], r["sc"], r["params"], r["torch"]
+    K = max(1, p.substreams)
+    s_local = (p.substream_end - p.substream_begin if K > 1 and p.substream_end > 0 else K) * r["S"] // K   # samples per pixel of this rank
+    import ctypes
+    rows = rtb.lib().rtb_render_local_rows(ctypes.byref(p))
+    spp_c = max(1, min(s_local, 4))
+    mk = p.flags & rtb.RENDER_MEGAKERNEL
+    pc = rtb.RenderParams(p.width, p.height, spp_c, p.row_begin, p.row_end, p.pixel0_seed, 0, 1 | mk,
                           p.interleave_count, p.interleave_index, p.interleave_rows)
     st = sc.render(p.width, p.height, spp_c, params=pc, want_accum=False, want_rgb=False)["stats"]
-    scale = r["S"] / spp_c
+    scale = s_local / spp_c
+    d_acc = torch.empty((rows, p.width, 3), dtype=torch.float32, device="cuda")
     if r["megakernel"]:
         box, tri = st["box_tests"] * scale, st["tri_tests"] * scale
-        kernel, kernel_ms, n_launch, other_ms = "k_render", r["kern_ms"], 1, 0.0
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        sc.render_device(p, d_accum=d_acc, d_rgb8=None, d_counters=None, stream=r["stream"])
+        e1.record()
+        torch.cuda.synchronize()
+        kernel, kernel_ms, n_launch, other_ms = "k_render", e0.elapsed_time(e1), 1, 0.0
     else:
         box, tri = (st["box_tests"] - st["light_box_tests"]) * scale, (st["tri_tests"] - st["light_tri_tests"]) * scale
-        pt = rtb.RenderParams(p.width, p.height, p.samples, p.row_begin, p.row_end, p.pixel0_seed, 0, rtb.RENDER_STAGE_TIMES,
-                              p.interleave_count, p.interleave_index, p.interleave_rows)
-        sc.render_device(pt, d_accum=None, d_rgb8=r["d_rgb"], d_counters=None, stream=r["stream"])
+        pt = rtb.RenderParams.from_buffer_copy(p)
+        pt.flags |= rtb.RENDER_STAGE_TIMES
+        sc.render_device(pt, d_accum=d_acc, d_rgb8=None, d_counters=None, stream=r["stream"])
         kernel_ms, other_ms, n_launch = sc.stage_ms()
         kernel = "k_wf_trace"
     bytes_all = 28.0 * box + 36.0 * tri
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
-        peak, src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+        hbm_peak, hbm_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
     else:
-        peak, src = 6650.0, "fallback 6.65 TB/s (of fallback)"
+        hbm_peak, hbm_src = 6650.0, "fallback 6.65 TB/s (of fallback)"
     achieved = bytes_all / (kernel_ms * 1e-3) * 1e-9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
-        t = json.load(open(tpath)).get(r["name"])
+        t = json.load(open(tpath)).get(r["scene"])
         traffic = t.get("dram_bytes_per_launch") if t else None
-    n_samples = r["n_local"] * r["W"] * r["S"]
+    n_samples = rows * r["W"] * s_local
     rays = max(1.0, st["closest_hit_rays"] * scale)
-    # the L2 figures the L2-resident scenes are really up against (SURVEY.md 8d): measured here, on this GPU
+    l2_bytes = torch.cuda.get_device_properties(sc.device).L2_cache_size
+    trav = sc.traversal_bytes
+    resident = trav <= l2_bytes
     l2 = None
-    try:
+    try:   # the figures the traversal is really up against, measured here, on this GPU
         stream_gbs, gather_gbs = rtb.measure_l2(sc.device, 32 << 20)
         l2 = {"stream_gbs": stream_gbs, "gather64_gbs": gather_gbs, "frac_of_stream": achieved / stream_gbs, "frac_of_gather64": achieved / gather_gbs,
               "how": "rtb_measure_l2: 32 MB buffer, coalesced 16-byte loads / 64-byte records at random indices (2 x LDG.256)"}
+        if not resident:
+            hs_gbs, hg_gbs = rtb.measure_l2(sc.device, 1 << 30)
+            l2["hbm_stream_gbs"], l2["hbm_gather64_gbs"], l2["frac_of_hbm_gather64"] = hs_gbs, hg_gbs, achieved / hg_gbs
     except Exception as e:   # a measurement aid: never fails the bench
         l2 = {"error": str(e)}
-    return {"bound": "hbm", "l2": l2, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+    if resident and l2 and "gather64_gbs" in l2:
+        bound, peak, src = "l2", l2["gather64_gbs"], "measured in this run: 64-byte records gathered at random indices from a 32 MB (L2-resident) buffer, rtb_measure_l2"
+        note = ("traversal set %.1f MB <= L2 %.0f MB: the kernel's fetches are served by the L2 (SURVEY.md 8d regime 1), so frac = achieved / the measured "
+                "L2 random-gather rate; frac_hbm is the same bytes over the HBM peak (not the binding limit)" % (trav / 1e6, l2_bytes / 1e6))
+    else:
+        bound, peak, src = "hbm", hbm_peak, hbm_src
+        note = "traversal set %.1f MB > L2 %.0f MB: HBM-bound regime (SURVEY.md 8d regime 2), frac = achieved / measured HBM peak" % (trav / 1e6, l2_bytes / 1e6)
+    return {"bound": bound, "l2": l2, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "frac_hbm": achieved / hbm_peak,
+            "hbm_peak": hbm_peak, "traffic": traffic,
             "kernel": kernel, "kernel_launches": int(n_launch), "kernel_ms_total": kernel_ms, "kernel_ms_avg": kernel_ms / max(1, n_launch),
             "kernel_share_of_step": kernel_ms / max(1e-9, kernel_ms + other_ms), "other_kernels_ms_total": other_ms,
             "algorithmic_bytes_per_launch": bytes_all / max(1, n_launch), "peak_source": src,
             "box_tests_per_ray": box / rays, "tri_tests_per_ray": tri / rays, "kernel_mrays_per_s": rays / (kernel_ms * 1e-3) * 1e-6,
-            "bytes_per_sample": bytes_all / max(1, n_samples),
-            "note": "scene traversal set (%.1f MB) is L2-resident: the HBM peak is the contract's denominator, not the binding limit; "
-                    "see DESIGN.md" % (sc.traversal_bytes / 1e6)}
+            "bytes_per_sample": bytes_all / max(1, n_samples), "traversal_bytes": int(trav), "l2_bytes": int(l2_bytes), "note": note}
 
 
 def main():
@@ -350,7 +384,7 @@ def main():
             "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": r["world"], "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic (stand-in scene from the seeded generator scenes/gen_scenes.py; the reference's geometry buffers were never shipped)",
-            "config": {"workload": r["name"], "parallelism": "row-block interleave x%d, NCCL all_gather of RGB8 rows" % r["world"],
+            "config": {"workload": r["name"], "parallelism": r["parallelism"],
                        "l2": "256 MB buffer written between timed steps (L2 flush)", "ray_depth": 6},
             "mrays_per_s": r["rays_per_step"] / (r["ms_per_step"] * 1e-3) * 1e-6,
             "light_pdf_mqueries_per_s": r["lq_per_step"] / (r["ms_per_step"] * 1e-3) * 1e-6,
@@ -358,7 +392,7 @@ def main():
             "clocks": r["clocks"],
             "e2e": {"value": r["e2e_value"], "unit": UNIT, "h2d_bytes_per_step": int(r["upload_bytes"]) * r["world"],
                     "d2h_bytes_per_step": r["W"] * r["H"] * 3},
-            "gpu_launches": int(r["launches"]) * r["world"],
+            "gpu_launches": int(r["launches"]),
             "roofline": roof,
         }
         if r["world"] == 1 and not args.no_cpu_baseline:

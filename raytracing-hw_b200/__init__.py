@@ -12,7 +12,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librtb.so")
+# RTB_LIB: another build of the same library (A/B runs of kernel variants, tools/gpu_run.sh variants)
+LIB_PATH = os.environ.get("RTB_LIB") or os.path.join(_HERE, "librtb.so")
 
 RTB_OK, RTB_ERR_INVALID, RTB_ERR_NO_DEVICE, RTB_ERR_CUDA, RTB_ERR_IO = 0, 1, 2, 3, 4
 CULL_REFERENCE, CULL_GLOBAL = 0, 1

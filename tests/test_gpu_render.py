@@ -122,8 +122,8 @@ def test_render_vs_reference_deterministic(name, size, spp, ref):
     out = rtb.Scene(hs, 0).render(W, H, spp, pixel0_seed=1)
     rgb, acc, _ = ref.RefScene.from_gltf(p, W, H, spp).render_deterministic(pixel0_seed=1)
     same = np.all(out["accum"] == acc, axis=-1)
-    assert same.mean() >= 0.999, "only %.5f of the pixels are bit-identical" % same.mean()
-    assert _util.rmse8(out["rgb"], rgb) <= 1.0
+    assert same.all(), "%d of %d pixels are not bit-identical (first at %s)" % (np.count_nonzero(~same), same.size, np.argwhere(~same)[:3].tolist())
+    assert np.array_equal(out["rgb"], rgb)
 
 
 @pytest.mark.ref
