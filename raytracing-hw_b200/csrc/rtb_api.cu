@@ -198,6 +198,8 @@ class Uploader {
                       cudaHostAlloc(&stage.buf[1], kBuf, cudaHostAllocPortable) == cudaSuccess;
             if (!ok) {   // no pinned memory to be had: plain copies
                 cudaGetLastError();
+                if (stage.buf[0]) { cudaFreeHost(stage.buf[0]); stage.buf[0] = nullptr; }
+                stage.buf[1] = nullptr;
                 for (auto &p : pieces_) if (p.bytes) RTB_CUDA(cudaMemcpy((char *) base_ + p.off, p.src, p.bytes, cudaMemcpyHostToDevice));
                 for (auto &p : pieces_) sc->upload_bytes += p.bytes;
                 return RTB_OK;
@@ -205,13 +207,14 @@ class Uploader {
             stage.ok = true;
         }
         // streams and events belong to a device: made per call (cheap)
-        RTB_CUDA(cudaStreamCreateWithFlags(&stage.st, cudaStreamNonBlocking));
-        for (auto &e : stage.ev) RTB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        cudaError_t err = cudaStreamCreateWithFlags(&stage.st, cudaStreamNonBlocking);
+        if (err != cudaSuccess) { stage.st = nullptr; RTB_CUDA(err); }
+        stage.ev[0] = stage.ev[1] = nullptr;
+        for (auto &e : stage.ev) if (err == cudaSuccess) err = cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
         int k = 0;
         bool used[2] = {false, false};
-        cudaError_t err = cudaSuccess;
         for (auto &p : pieces_) {
-            for (size_t done = 0; done < p.bytes && err == cudaSuccess; done += kBuf) {
+            for (size_t done = 0; done < p.bytes && err == cudaSuccess; done += kBuf) {   // (nothing runs once err is set)
                 const size_t m = std::min(kBuf, p.bytes - done);
                 if (used[k]) err = cudaEventSynchronize(stage.ev[k]);
                 parallel_copy(stage.buf[k], (const char *) p.src + done, m);
@@ -223,7 +226,7 @@ class Uploader {
             sc->upload_bytes += p.bytes;
         }
         if (err == cudaSuccess) err = cudaStreamSynchronize(stage.st);
-        for (auto &e : stage.ev) cudaEventDestroy(e);
+        for (auto &e : stage.ev) if (e) cudaEventDestroy(e);
         cudaStreamDestroy(stage.st);
         RTB_CUDA(err);
         return RTB_OK;
@@ -348,9 +351,14 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
     sc->d.n_meshes = L.n_meshes;
     fill_scalars(desc, sc->d);
 
-    RTB_CUDA(cudaMalloc((void **) &sc->queue_heads, kQueueHeads * sizeof(unsigned)));
-    for (auto &s : sc->streams) RTB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
-    for (auto &e : sc->ev) RTB_CUDA(cudaEventCreate(&e));
+    // (failures from here on still go through fail(): the scene and its device arena are released)
+    cudaError_t ce = cudaMalloc((void **) &sc->queue_heads, kQueueHeads * sizeof(unsigned));
+    for (auto &s : sc->streams) if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking);
+    for (auto &e : sc->ev) if (ce == cudaSuccess) ce = cudaEventCreate(&e);
+    if (ce != cudaSuccess) {
+        rtb::set_error(std::string("rtb_scene_create: ") + cudaGetErrorString(ce));
+        return fail(RTB_ERR_CUDA);
+    }
     *out = sc;
     return RTB_OK;
 }
@@ -558,9 +566,15 @@ int rtb_render_resume_device(rtb_scene *scene, const rtb_render_params *p, void 
             RTB_CUDA(cudaEventCreateWithFlags(&scene->wf_streams.fork, cudaEventDisableTiming));
             scene->wf_streams_ok = true;
         }
-        rtb::launch_render_wavefront(scene->d, L, scene->wf_state, (cudaStream_t) stream, &scene->launches,
-                                     timed ? &scene->stage_events : nullptr, &scene->wf_streams);
-        scene->stage_events_valid = timed;
+        const int wrc = rtb::launch_render_wavefront(scene->d, L, scene->wf_state, (cudaStream_t) stream, &scene->launches,
+                                                     timed ? &scene->stage_events : nullptr, &scene->wf_streams);
+        scene->stage_events_valid = timed && wrc == 0;
+        if (wrc != 0) {
+            const cudaError_t e = cudaGetLastError();
+            rtb::set_error(wrc == 2 ? "rtb_render_device: the frame did not finish (slots still live after the bounded number of extra rounds)"
+                                    : std::string("rtb_render_device: stream synchronisation failed: ") + cudaGetErrorString(e));
+            return RTB_ERR_CUDA;
+        }
     }
     RTB_CUDA(cudaGetLastError());
     return RTB_OK;

@@ -59,8 +59,9 @@ struct WfStreams {   // owned by the scene: one stream per slot group + fork / j
     int (*progress)(int, void *) = nullptr;
     void *progress_user = nullptr;
 };
-void launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *state, cudaStream_t stream, unsigned long long *launches,
-                             std::vector<cudaEvent_t> *stage_events, WfStreams *aux);
+// returns 0, 1 (a stream synchronisation failed) or 2 (slots still live after the bounded number of extra rounds)
+int launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *state, cudaStream_t stream, unsigned long long *launches,
+                            std::vector<cudaEvent_t> *stage_events, WfStreams *aux);
 void launch_resolve(const float *d_accum, size_t n_pixels, int samples, uint8_t *d_rgb8, cudaStream_t stream);
 
 }  // namespace rtb

@@ -282,9 +282,10 @@ int wf_groups(unsigned n_slots, bool light_scene) {
 // independent, so the tail of one group's queue kernel (lanes running dry one by one) and its latency-bound shade
 // kernel overlap the other group's ALU-bound queue kernel.  With stage timing on, one group on the caller's stream:
 // a kernel's duration is only defined when it runs alone.
-void launch_render_wavefront(const DScene &sc, const RenderLaunch &p_in, void *state, cudaStream_t stream, unsigned long long *launches,
-                             std::vector<cudaEvent_t> *stage_events, WfStreams *aux) {
-    if (p_in.local_rows <= 0 || p_in.width <= 0 || p_in.samples <= 0) return;
+int launch_render_wavefront(const DScene &sc, const RenderLaunch &p_in, void *state, cudaStream_t stream, unsigned long long *launches,
+                            std::vector<cudaEvent_t> *stage_events, WfStreams *aux) {
+    if (p_in.local_rows <= 0 || p_in.width <= 0 || p_in.samples <= 0) return 0;
+    int status = 0;
     RenderLaunch p = p_in;
     if (p.substreams <= 1) { p.substreams = 1; p.sub_begin = 0; p.sub_end = 1; }
     p.plane_slots = wf_plane_slots(p);
@@ -518,6 +519,7 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p_in, void *s
         // Suspended rays cost their slots extra iterations: compact (that counts the live slots), read the counts back,
         // and go on in rounds of 16 until every list is empty.  The margin above makes one read-back the normal case.
         long long it = iterations;
+        status = 2;   // until a read-back says every list is empty
         for (int round = 0; round < 4096; ++round) {
             unsigned live[kWfMaxGroups];
             for (int g = 0; g < G; ++g) {
@@ -525,10 +527,10 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p_in, void *s
                 cudaMemcpyAsync(&live[g], grp[g].n_list[grp[g].cur], sizeof(unsigned), cudaMemcpyDeviceToHost, grp[g].st);
             }
             join();
-            if (cudaStreamSynchronize(stream) != cudaSuccess) break;   // (the caller sees the error)
+            if (cudaStreamSynchronize(stream) != cudaSuccess) { status = 1; break; }
             unsigned total = 0;
             for (int g = 0; g < G; ++g) total += live[g];
-            if (total == 0) break;
+            if (total == 0) { status = 0; break; }
             if (G > 1) {
                 cudaEventRecord(aux->fork, stream);
                 for (int g = 0; g < G; ++g) cudaStreamWaitEvent(grp[g].st, aux->fork, 0);
@@ -547,8 +549,12 @@ void launch_render_wavefront(const DScene &sc, const RenderLaunch &p_in, void *s
         cudaStreamSynchronize(stream);
         prog_call(100);
     }
-    if (stage_events) stage_events->resize(ev_i);   // (events beyond ev_i were created by an earlier, longer frame)
+    if (stage_events) {   // events beyond ev_i were created by an earlier, longer frame
+        for (size_t i = ev_i; i < stage_events->size(); ++i) cudaEventDestroy((*stage_events)[i]);
+        stage_events->resize(ev_i);
+    }
     if (launches) *launches += nl;
+    return status;
 }
 
 }  // namespace rtb

@@ -376,7 +376,11 @@ void load_gltf(const std::string &filename, int width, int height, int samples, 
         const size_t packed = comps * csize;
         const size_t bs = (size_t) bv.number_or("byteStride", 0);
         v.stride = bs ? bs : packed;
-        if (v.count && packed && start + (v.count - 1) * v.stride + packed > buf.size()) throw std::runtime_error("[gltf check] accessor out of range");
+        // count elements of `packed` bytes, `stride` apart, must lie inside the buffer (no wrap-around for huge counts)
+        if (v.count && packed) {
+            const size_t room = buf.size() - start;
+            if (packed > room || v.stride == 0 || v.count - 1 > (room - packed) / v.stride) throw std::runtime_error("[gltf check] accessor out of range");
+        }
         return v;
     };
     auto image_of = [&](const Json *tex_info) -> int {
@@ -478,6 +482,9 @@ void load_gltf(const std::string &filename, int width, int height, int samples, 
                         index[v] = x;
                     }
                 }
+                for (int v = 0; v < 3; ++v)   // (the reference indexes the raw buffers unchecked: scene_parser.cpp:306-343)
+                    if (index[v] >= pos.count || (nv && index[v] >= nrm.count) || (tv && index[v] >= uv.count) || (gv && index[v] >= tan.count))
+                        throw std::runtime_error("[gltf check] vertex index out of range");
                 const size_t t = base + i;
                 float P[3][4];
                 for (int v = 0; v < 3; ++v) {

@@ -63,7 +63,8 @@ void build_bvh(HostTriangles &tris, HostBvh &out, int threads = 0);
 // parse_scene_gltf (src/io/scene_parser.cpp:25-350); throws std::runtime_error like the reference.
 void load_gltf(const std::string &path, int width, int height, int samples, HostScene &scene);
 
-// PNG (own decoder, zlib) -> RGBA8.  JPEG is supported only when the build found stb_image.h (RTB_HAVE_STB).
+// PNG (image_decode.cpp, zlib) or baseline JPEG (jpeg_decode.cpp) -> RGBA8, the bytes tinygltf / stb_image give.
 bool decode_image(const std::vector<uint8_t> &bytes, HostTexture &out, std::string &err);
+bool decode_jpeg(const std::vector<uint8_t> &bytes, HostTexture &out, std::string &err);
 
 }  // namespace rtb

@@ -1,22 +1,21 @@
 // Image decode for glTF textures -> RGBA8 (what tinygltf/stb_image hand the reference: always 4 channels, 8 bit,
 // thirdparty/tinygltf/tiny_gltf.h:2609,2681-2683; scene_parser.cpp:131-142 rejects anything but 8 bits).
-//   * PNG: own decoder on top of zlib's inflate (8/16-bit, grey / RGB / palette / grey+alpha / RGBA, interlace 0).
+//   * PNG: own decoder on top of zlib's inflate (1-8 bit, grey / RGB / palette / grey+alpha / RGBA, tRNS, interlace 0).
 //     16-bit samples are not "8 bit" for the reference (it throws); we throw the same message.
-//   * JPEG & co: only when the build found an stb_image.h to include (RTB_HAVE_STB, see build.sh) -- stb_image is
-//     what tinygltf itself calls, so the bytes match the reference's; otherwise a clear error.
+//   * JPEG: own baseline decoder (jpeg_decode.cpp) restating stb_image's integer arithmetic, so the bytes equal the
+//     reference's (tests/test_formats.py compares both decoders with the compiled reference).
+// ONE decode path per format, the same in every build: nothing here depends on files outside this repository.
 #include "host_scene.h"
 
+#include <algorithm>
 #include <cstring>
+#include <string>
 #include <zlib.h>
-
-#ifdef RTB_HAVE_STB
-#define STB_IMAGE_IMPLEMENTATION
-#define STBI_NO_STDIO
-#include <stb_image.h>
-#endif
 
 namespace rtb {
 namespace {
+
+constexpr uint32_t kMaxTextureSide = 32768;   // sanity limit on either side of an image
 
 uint32_t be32(const uint8_t *p) { return ((uint32_t) p[0] << 24) | ((uint32_t) p[1] << 16) | ((uint32_t) p[2] << 8) | p[3]; }
 
@@ -57,6 +56,7 @@ bool decode_png(const std::vector<uint8_t> &bytes, HostTexture &out, std::string
         p += 12 + (size_t) len;
     }
     if (!seen_ihdr || w == 0 || h == 0) { err = "PNG without IHDR"; return false; }
+    if (w > kMaxTextureSide || h > kMaxTextureSide) { err = "PNG larger than " + std::to_string(kMaxTextureSide) + " pixels a side"; return false; }
     if (interlace != 0) { err = "interlaced PNG not supported"; return false; }
     if (depth == 16) { err = "Texture format not supported: only 8 bit channels are supported"; return false; }
     if (depth != 8 && !(ctype == 0 || ctype == 3)) { err = "unsupported PNG bit depth"; return false; }
@@ -77,12 +77,29 @@ bool decode_png(const std::vector<uint8_t> &bytes, HostTexture &out, std::string
         z_stream zs;
         std::memset(&zs, 0, sizeof(zs));
         if (inflateInit(&zs) != Z_OK) { err = "zlib init failed"; return false; }
-        zs.next_in = idat.data();
-        zs.avail_in = (uInt) idat.size();
-        zs.next_out = raw.data();
-        zs.avail_out = (uInt) raw.size();
-        const int rc = inflate(&zs, Z_FINISH);
-        const size_t got = raw.size() - zs.avail_out;
+        // zlib's counters are 32 bit: feed and drain in pieces of at most 1 GB
+        const size_t kPiece = (size_t) 1 << 30;
+        size_t in_off = 0, out_off = 0;
+        int rc = Z_OK;
+        while (rc == Z_OK) {
+            if (zs.avail_in == 0 && in_off < idat.size()) {
+                const size_t m = std::min(kPiece, idat.size() - in_off);
+                zs.next_in = idat.data() + in_off;
+                zs.avail_in = (uInt) m;
+                in_off += m;
+            }
+            if (zs.avail_out == 0 && out_off < raw.size()) {
+                const size_t m = std::min(kPiece, raw.size() - out_off);
+                zs.next_out = raw.data() + out_off;
+                zs.avail_out = (uInt) m;
+                out_off += m;
+            }
+            const bool last = in_off >= idat.size();
+            rc = inflate(&zs, last ? Z_FINISH : Z_NO_FLUSH);
+            if (rc == Z_BUF_ERROR && zs.avail_out == 0 && out_off >= raw.size()) break;   // all rows are there
+            if (rc == Z_BUF_ERROR && (zs.avail_in == 0 && !last)) rc = Z_OK;
+        }
+        const size_t got = out_off - zs.avail_out;
         inflateEnd(&zs);
         if ((rc != Z_STREAM_END && rc != Z_OK && rc != Z_BUF_ERROR) || got != raw.size()) { err = "PNG inflate failed"; return false; }
     }
@@ -117,7 +134,11 @@ bool decode_png(const std::vector<uint8_t> &bytes, HostTexture &out, std::string
         uint8_t *dst = &out.rgba[(size_t) y * w * 4];
         for (uint32_t x = 0; x < w; ++x) {
             uint8_t r, g, b, a = 255;
-            if (ctype == 2) { r = cur[x * 3]; g = cur[x * 3 + 1]; b = cur[x * 3 + 2]; }
+            if (ctype == 2) {
+                r = cur[x * 3]; g = cur[x * 3 + 1]; b = cur[x * 3 + 2];
+                // tRNS colour key (16-bit big-endian per channel; 8-bit images use the low byte)
+                if (trns.size() >= 6 && r == trns[1] && g == trns[3] && b == trns[5]) a = 0;
+            }
             else if (ctype == 6) { r = cur[x * 4]; g = cur[x * 4 + 1]; b = cur[x * 4 + 2]; a = cur[x * 4 + 3]; }
             else if (ctype == 4) { r = g = b = cur[x * 2]; a = cur[x * 2 + 1]; }
             else {
@@ -134,6 +155,7 @@ bool decode_png(const std::vector<uint8_t> &bytes, HostTexture &out, std::string
                 } else {
                     const unsigned maxv = (1u << depth) - 1u;
                     r = g = b = (uint8_t) (s * 255u / maxv);
+                    if (trns.size() >= 2 && s == ((((unsigned) trns[0] << 8) | trns[1]) & maxv)) a = 0;   // grey colour key
                 }
             }
             dst[x * 4] = r; dst[x * 4 + 1] = g; dst[x * 4 + 2] = b; dst[x * 4 + 3] = a;
@@ -145,25 +167,10 @@ bool decode_png(const std::vector<uint8_t> &bytes, HostTexture &out, std::string
 }  // namespace
 
 bool decode_image(const std::vector<uint8_t> &bytes, HostTexture &out, std::string &err) {
-#ifdef RTB_HAVE_STB
-    (void) decode_png;   // with stb_image available every format goes through it, exactly as in tinygltf
-    int w = 0, h = 0, comp = 0;
-    if (stbi_is_16_bit_from_memory(bytes.data(), (int) bytes.size())) {
-        err = "Texture format not supported: only 8 bit channels are supported";
-        return false;
-    }
-    unsigned char *px = stbi_load_from_memory(bytes.data(), (int) bytes.size(), &w, &h, &comp, 4);
-    if (!px) { err = std::string("stb_image: ") + stbi_failure_reason(); return false; }
-    out.width = w;
-    out.height = h;
-    out.rgba.assign(px, px + (size_t) w * h * 4);
-    stbi_image_free(px);
-    return true;
-#else
     if (bytes.size() >= 8 && bytes[0] == 0x89 && bytes[1] == 'P') return decode_png(bytes, out, err);
-    err = "only PNG textures are supported by this build (no stb_image.h was available when it was compiled)";
+    if (bytes.size() >= 4 && bytes[0] == 0xff && bytes[1] == 0xd8) return decode_jpeg(bytes, out, err);
+    err = "unknown image format (PNG and baseline JPEG are supported)";
     return false;
-#endif
 }
 
 }  // namespace rtb
