@@ -25,6 +25,22 @@
 #define RTB_RING_WAVEFRONT 0
 #endif
 
+// Latency experiments of round 2 (each a build-time switch so that variants can be A/B-ed on the box, tools/gpu_run.sh variants):
+//   RTB_PREFETCH_LEAF    : while triangle i of a leaf is tested, prefetch.global.L1 the record of triangle i + 1 (the
+//                          triangles of a leaf are contiguous and are all tested: its address is known a step ahead)
+//   RTB_PREFETCH_SIBLING : at a push, prefetch the deferred sibling's record
+//   RTB_TRACE_STATE_CS   : the queue kernel's path-state traffic (ray in, hit out) with evict-first (.cs) hints, so that
+//                          streaming state stops displacing BVH records from the L1
+#ifndef RTB_PREFETCH_LEAF
+#define RTB_PREFETCH_LEAF 0
+#endif
+#ifndef RTB_PREFETCH_SIBLING
+#define RTB_PREFETCH_SIBLING 0
+#endif
+#ifndef RTB_TRACE_STATE_CS
+#define RTB_TRACE_STATE_CS 0
+#endif
+
 namespace rtb {
 
 constexpr int kRingThreads = 128;   // threads per CTA of the kernels that run the form-3 loop
@@ -357,6 +373,8 @@ struct LaneTraversal {
 };
 
 #ifdef __CUDACC__
+__device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 // 32 bytes through the read-only path in one instruction (p 32-byte aligned)
 __device__ __forceinline__ void ldg256(const float4 *p, float4 &lo, float4 &hi) {
     asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
@@ -445,7 +463,20 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
             int4 d;
             ldg256(p, a, bb);
             ldg256(p + 2, c, d);
+#if RTB_PREFETCH_LEAF
+            // the next triangle of the leaf (if any) will be fetched by this lane's next step whatever this test says
+            if (doL && (unsigned) (L.link - 0x0FFFFFFF) >= LaneTraversal<COUNT, RING>::kLeafBusy) prefetch_l1(p + kTriStride);
+#endif
+#if RTB_PREFETCH_SIBLING
+            const int sp_before = L.sp;
+#endif
             if (doN) L.node_compute3(a, bb, c, d, cnt);
+#if RTB_PREFETCH_SIBLING
+            if (doN && L.sp > sp_before) {   // a sibling was deferred: it is needed when this subtree is done
+                const int dl = L.entry3(L.sp - 1).x;
+                prefetch_l1(dl >= 0 ? reinterpret_cast<const float4 *>(b.nodes + dl) : b.tris + (size_t) (dl & 0x0FFFFFFF) * kTriStride);
+            }
+#endif
             if (doL) L.tri_compute3(a, bb, c, cnt);
         }
         if (tail_steps > 0) {

@@ -60,7 +60,15 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(const __grid_constant__ 
             if (e & kSlotDone) return 0;
             tag = i;
             const unsigned slot = e & kSlotIndex;
+#if RTB_TRACE_STATE_CS
+            {
+                const float4 ra = __ldcs(w.ray_a + slot);
+                const float2 rb = __ldcs(w.ray_b + slot);
+                make_ray(L.r, ra.x, ra.y, ra.z, ra.w, rb.x, rb.y);
+            }
+#else
             wf_load_ray(w, slot, L.r);
+#endif
             if (e & kSlotSuspended) {
                 L.load3(w.susp + (size_t) slot * w.susp_stride);
                 return 2;
@@ -69,7 +77,11 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(const __grid_constant__ 
         },
         [&](unsigned i, const Ray &, const Hit &h) {
             const unsigned e = list[i];
+#if RTB_TRACE_STATE_CS
+            __stcs(w.hit + (e & kSlotIndex), make_float4(h.t, h.u, h.v, u2f((uint32_t) h.id)));
+#else
             w.hit[e & kSlotIndex] = make_float4(h.t, h.u, h.v, u2f((uint32_t) h.id));
+#endif
             if (e & kSlotSuspended) list[i] = e & ~kSlotSuspended;
         },
         [&](unsigned i, LaneTraversal<COUNT, RTB_RING_WAVEFRONT> &L) {
