@@ -168,6 +168,58 @@ void rtb_host_scene_destroy(rtb_host_scene *hs);
 
 /* Uploads the scene to CUDA device `device` (converts nodes to the 64-byte two-child layout). */
 int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out);
+
+/* ---- device-side scene assembly ------------------------------------------------------------
+ * The reference assembles every triangle on the host while it parses the file (src/io/scene_parser.cpp:280-345: index
+ * fetch, world transform, p0 / p1-p0 / p2-p0, normal transform + normalise, texcoords, tangents), computes the geometric
+ * normal lazily (src/geometry/primitive.cpp:77-84), and its 64-byte Node array is what BVH::intersect walks.
+ * rtb_scene_create_raw takes the geometry AS THE FILE DELIVERS IT -- one rtb_raw_mesh per glTF primitive, pointing at the
+ * raw accessor views -- plus the host builder's permutation, uploads those bytes unchanged and runs the assembly on the
+ * GPU: one kernel writes the traversal, shading and tangent records of every triangle with the host's operation order
+ * (every buffer is byte-equal to what rtb_scene_create builds from the host-assembled arrays:
+ * tests/test_gpu_assembly.py), and a level-by-level pass turns the reference-order nodes into the 64-byte two-child
+ * nodes.  desc->tri_pos / tri_nrm / tri_tan / tri_uv / tri_mesh are NOT read (they may be NULL); everything else in
+ * desc is as for rtb_scene_create (the light list is small and stays host-assembled).                                 */
+#define RTB_NORMALS_TRANSFORM 0   /* glTF: normalize(normal_transform * n)  (scene_parser.cpp:316-325); no view: (0,0,1) */
+#define RTB_NORMALS_VERBATIM 1    /* the view holds finished world-space normals                                         */
+#define RTB_NORMALS_FLAT 2        /* normalize(cross(U, V)) for all three vertices (no view)                             */
+#define RTB_RAW_WORLD_POSITIONS 1 /* rtb_raw_mesh::flags                                                                    */
+typedef struct rtb_raw_mesh {
+    uint32_t n_tris;              /* indices.count / 3                                                                  */
+    uint32_t n_vertices;          /* elements in each vertex view; every index must be below it                         */
+    const void *indices;          /* u16 / u32 index view, or NULL: triangle i uses vertices 3i, 3i+1, 3i+2            */
+    int32_t index_bytes;          /* 2 or 4 (0 with indices == NULL)                                                    */
+    int32_t index_stride;         /* bytes between indices (= index_bytes when tightly packed)                          */
+    const void *position;         /* float3 view; strides in bytes, multiples of 4; views 4-byte aligned                */
+    const void *normal;           /* float3 view or NULL                                                                */
+    const void *tangent;          /* float4 view or NULL (zeros)                                                        */
+    const void *texcoord;         /* float2 view or NULL (zeros)                                                        */
+    int32_t position_stride, normal_stride, tangent_stride, texcoord_stride;
+    int32_t normal_mode;          /* RTB_NORMALS_*                                                                      */
+    int32_t mesh_id;              /* Primitive::mesh_id of its triangles (index into desc->mesh_material / _normal_transform) */
+    int32_t flags;                /* RTB_RAW_WORLD_POSITIONS: positions are used as they are (no transform)             */
+    double transform[16];         /* node matrix, matrix4d data order (src/utils/matrix.h); positions go through
+                                     multiply(transform, vector4f): double products, FLOAT accumulator (matrix.h:66-73) */
+} rtb_raw_mesh;
+typedef struct rtb_raw_geometry {
+    uint32_t n_meshes;
+    const rtb_raw_mesh *meshes;   /* in loader order: mesh m's triangles are numbered after those of meshes 0..m-1      */
+    const uint32_t *tri_source;   /* desc->n_tris entries: post-build triangle i is loader-order triangle tri_source[i]
+                                     (BVH::buildBVH reorders Scene::objects, src/core/bvh.cpp:50,110)                   */
+} rtb_raw_geometry;
+/* the raw views of a host scene (valid until rtb_host_scene_destroy), and -- desc != NULL -- the scene description that
+ * goes with them: as rtb_host_scene_desc fills it, but tri_nrm / tri_tan / tri_uv stay NULL (the host never assembles them) */
+int rtb_host_scene_raw_geometry(const rtb_host_scene *hs, rtb_scene_desc *desc, rtb_raw_geometry *raw);
+int rtb_scene_create_raw(const rtb_scene_desc *desc, const rtb_raw_geometry *raw, int device, rtb_scene **out);
+/* Test / inspection aid: copies device buffer `which` of a scene to the host (dst may be NULL: size query).  Returns the
+ * buffer's size in bytes through *bytes; copies min(*bytes on entry, size).                                            */
+#define RTB_BUF_NODES 0
+#define RTB_BUF_TRIS 1
+#define RTB_BUF_SHADE 2
+#define RTB_BUF_TANGENTS 3
+#define RTB_BUF_BIG_LEAVES 4
+#define RTB_BUF_BVH_SCALARS 5     /* root_box[6] (float), root_link, n_internal, n_tris, max_depth (int32): 40 bytes     */
+int rtb_scene_read_buffer(rtb_scene *scene, int which, void *dst, size_t *bytes);
 void rtb_scene_destroy(rtb_scene *scene);
 int rtb_scene_device(const rtb_scene *scene);
 /* bytes of device memory holding nodes+triangles (the traversal working set) */

@@ -25,6 +25,7 @@ ABI_SYMBOLS = [
     "rtb_last_error", "rtb_device_count",
     "rtb_host_scene_load_gltf", "rtb_host_scene_from_triangles", "rtb_host_scene_desc", "rtb_host_scene_bvh_stats",
     "rtb_host_scene_build_seconds", "rtb_host_scene_destroy",
+    "rtb_host_scene_raw_geometry", "rtb_scene_create_raw", "rtb_scene_read_buffer",
     "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_device", "rtb_scene_traversal_bytes", "rtb_scene_upload_bytes", "rtb_scene_launches", "rtb_scene_stage_ms",
     "rtb_closest_hit", "rtb_closest_hit_device", "rtb_light_pdf", "rtb_measure_l2",
     "rtb_render", "rtb_render_device", "rtb_resolve_device", "rtb_render_local_rows", "rtb_render_global_row",
@@ -54,6 +55,23 @@ class SceneDesc(C.Structure):
         ("cam_pos", C.c_float * 3), ("cam_axes", C.c_float * 9), ("cam_tan_half_fov", C.c_float * 2),
         ("ray_depth", C.c_int32), ("max_distance", C.c_float), ("bg_color", C.c_float * 3),
     ]
+
+
+class RawMesh(C.Structure):   # rtb_raw_mesh
+    _fields_ = [("n_tris", C.c_uint32), ("n_vertices", C.c_uint32), ("indices", C.c_void_p), ("index_bytes", C.c_int32),
+                ("index_stride", C.c_int32), ("position", C.c_void_p), ("normal", C.c_void_p), ("tangent", C.c_void_p),
+                ("texcoord", C.c_void_p), ("position_stride", C.c_int32), ("normal_stride", C.c_int32),
+                ("tangent_stride", C.c_int32), ("texcoord_stride", C.c_int32), ("normal_mode", C.c_int32),
+                ("mesh_id", C.c_int32), ("flags", C.c_int32), ("transform", C.c_double * 16)]
+
+
+class RawGeometry(C.Structure):   # rtb_raw_geometry
+    _fields_ = [("n_meshes", C.c_uint32), ("meshes", C.POINTER(RawMesh)), ("tri_source", C.c_void_p)]
+
+
+NORMALS_TRANSFORM, NORMALS_VERBATIM, NORMALS_FLAT = 0, 1, 2
+RAW_WORLD_POSITIONS = 1
+BUF_NODES, BUF_TRIS, BUF_SHADE, BUF_TANGENTS, BUF_BIG_LEAVES, BUF_BVH_SCALARS = range(6)
 
 
 class RenderParams(C.Structure):
@@ -110,6 +128,9 @@ def lib():
         L.rtb_host_scene_destroy.argtypes = [C.c_void_p]
         L.rtb_host_scene_destroy.restype = None
         L.rtb_scene_create.argtypes = [C.POINTER(SceneDesc), C.c_int, C.POINTER(C.c_void_p)]
+        L.rtb_host_scene_raw_geometry.argtypes = [C.c_void_p, C.POINTER(SceneDesc), C.POINTER(RawGeometry)]
+        L.rtb_scene_create_raw.argtypes = [C.POINTER(SceneDesc), C.POINTER(RawGeometry), C.c_int, C.POINTER(C.c_void_p)]
+        L.rtb_scene_read_buffer.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_size_t)]
         L.rtb_scene_destroy.argtypes = [C.c_void_p]
         L.rtb_scene_destroy.restype = None
         L.rtb_scene_device.argtypes = [C.c_void_p]
@@ -174,8 +195,29 @@ class HostScene:
 
     def __init__(self, handle):
         self.h = C.c_void_p(handle)
-        self.desc = SceneDesc()
-        _check(lib().rtb_host_scene_desc(self.h, C.byref(self.desc)))
+        self._desc = None
+        self._raw = None
+
+    @property
+    def desc(self):
+        """the flat description (rtb_host_scene_desc): normals / tangents / texcoords are assembled on the HOST at the first use"""
+        if self._desc is None:
+            d = SceneDesc()
+            _check(lib().rtb_host_scene_desc(self.h, C.byref(d)))
+            self._desc = d
+        return self._desc
+
+    def raw(self):
+        """(SceneDesc without host-assembled attributes, RawGeometry): what rtb_scene_create_raw takes"""
+        if self._raw is None:
+            d, g = SceneDesc(), RawGeometry()
+            _check(lib().rtb_host_scene_raw_geometry(self.h, C.byref(d), C.byref(g)))
+            self._raw = (d, g)
+        return self._raw
+
+    def tri_source(self):
+        d, g = self.raw()
+        return _np_view(g.tri_source, (d.n_tris,), np.uint32)
 
     @classmethod
     def load_gltf(cls, path, width, height, samples):
@@ -255,13 +297,30 @@ class HostScene:
 class Scene:
     """Device-resident scene on one GPU; the drop-in for BVH::intersect and Scene::render."""
 
-    def __init__(self, host_scene_or_desc, device=0):
-        desc = host_scene_or_desc.desc if isinstance(host_scene_or_desc, HostScene) else host_scene_or_desc
-        self._keep = host_scene_or_desc
+    def __init__(self, host_scene_or_desc, device=0, assembled=False, raw=None):
+        """A HostScene goes through rtb_scene_create_raw (the triangles are assembled on the GPU from the raw views) unless
+        assembled=True; a bare SceneDesc through rtb_scene_create (host-assembled arrays), or with raw= a RawGeometry."""
+        self._keep = (host_scene_or_desc, raw)
         h = C.c_void_p()
-        _check(lib().rtb_scene_create(C.byref(desc), device, C.byref(h)))
+        if isinstance(host_scene_or_desc, HostScene) and not assembled:
+            d, g = host_scene_or_desc.raw()
+            _check(lib().rtb_scene_create_raw(C.byref(d), C.byref(g), device, C.byref(h)))
+        elif raw is not None:
+            _check(lib().rtb_scene_create_raw(C.byref(host_scene_or_desc), C.byref(raw), device, C.byref(h)))
+        else:
+            desc = host_scene_or_desc.desc if isinstance(host_scene_or_desc, HostScene) else host_scene_or_desc
+            _check(lib().rtb_scene_create(C.byref(desc), device, C.byref(h)))
         self.h = h
         self.device = device
+
+    def read_buffer(self, which):
+        """device buffer `which` (BUF_*) as bytes (test / inspection aid)"""
+        n = C.c_size_t(0)
+        _check(lib().rtb_scene_read_buffer(self.h, which, None, C.byref(n)))
+        out = np.zeros(n.value, np.uint8)
+        if n.value:
+            _check(lib().rtb_scene_read_buffer(self.h, which, _ptr(out), C.byref(n)))
+        return out
 
     def close(self):
         if self.h:

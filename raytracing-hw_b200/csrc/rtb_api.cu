@@ -3,6 +3,7 @@
 #include "../../include/rtb.h"
 #include "rtb_kernels.cuh"
 #include "rtb_layout.hpp"
+#include "rtb_assemble.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -117,9 +118,10 @@ struct rtb_scene {
     rtb::DScene d;
     std::vector<std::pair<void *, size_t>> allocs;   // blocks from rtb::g_blocks
     size_t traversal_bytes = 0;
-    size_t upload_bytes = 0;
+    size_t upload_bytes = 0;   // host->device bytes copied by rtb_scene_create / rtb_scene_create_raw
+    size_t n_big = 0;          // entries of d.bvh.big_leaves
     unsigned *queue_heads = nullptr;   // kQueueHeads ray-queue cursors, rotated per launch (stream-ordered memset)
-    unsigned next_head = 0;   // host->device bytes copied by rtb_scene_create
+    unsigned next_head = 0;
     cudaStream_t streams[3] = {nullptr, nullptr, nullptr};
     cudaEvent_t ev[2] = {nullptr, nullptr};
     // staging buffers reused across calls
@@ -168,18 +170,20 @@ using namespace rtb;
 // thread: 66 ms for the 335 MB Sponza stand-in, measured (tools/e2e_probe.py); this path is part of bench.py's e2e step.
 class Uploader {
   public:
-    // returns the piece's index; *dst receives base + offset in run()
+    // *dst receives base + offset in alloc(); src == nullptr: the piece is only reserved (a kernel fills it)
     void add(const void *src, size_t bytes, const void **dst) {
         pieces_.push_back({src, bytes, total_, dst});
         total_ += (bytes + 255) / 256 * 256;
     }
     // allocates; pointers are valid (but their contents not yet copied) after this
-    int alloc(rtb_scene *sc) {
+    // temp: the block is not the scene's; the caller hands it back with release_temp() once the kernels that read it are done
+    int alloc(rtb_scene *sc, bool temp = false) {
         for (auto &p : pieces_) *p.dst = nullptr;
         if (total_ == 0) return RTB_OK;
         size_t got = 0;
         RTB_CUDA(rtb::g_blocks.acquire(sc->device, total_, &base_, &got));
-        sc->allocs.emplace_back(base_, got);
+        if (temp) got_ = got;
+        else sc->allocs.emplace_back(base_, got);
         for (auto &p : pieces_) if (p.bytes) *p.dst = (char *) base_ + p.off;
         return RTB_OK;
     }
@@ -200,8 +204,8 @@ class Uploader {
                 cudaGetLastError();
                 if (stage.buf[0]) { cudaFreeHost(stage.buf[0]); stage.buf[0] = nullptr; }
                 stage.buf[1] = nullptr;
-                for (auto &p : pieces_) if (p.bytes) RTB_CUDA(cudaMemcpy((char *) base_ + p.off, p.src, p.bytes, cudaMemcpyHostToDevice));
-                for (auto &p : pieces_) sc->upload_bytes += p.bytes;
+                for (auto &p : pieces_) if (p.bytes && p.src) RTB_CUDA(cudaMemcpy((char *) base_ + p.off, p.src, p.bytes, cudaMemcpyHostToDevice));
+                for (auto &p : pieces_) if (p.src) sc->upload_bytes += p.bytes;
                 return RTB_OK;
             }
             stage.ok = true;
@@ -214,6 +218,7 @@ class Uploader {
         int k = 0;
         bool used[2] = {false, false};
         for (auto &p : pieces_) {
+            if (!p.src) continue;
             for (size_t done = 0; done < p.bytes && err == cudaSuccess; done += kBuf) {   // (nothing runs once err is set)
                 const size_t m = std::min(kBuf, p.bytes - done);
                 if (used[k]) err = cudaEventSynchronize(stage.ev[k]);
@@ -230,6 +235,12 @@ class Uploader {
         cudaStreamDestroy(stage.st);
         RTB_CUDA(err);
         return RTB_OK;
+    }
+
+    void release_temp(rtb_scene *sc) {
+        if (base_ && got_) rtb::g_blocks.release(sc->device, base_, got_);
+        base_ = nullptr;
+        got_ = 0;
     }
 
   private:
@@ -255,6 +266,7 @@ class Uploader {
     std::vector<P> pieces_;
     size_t total_ = 0;
     void *base_ = nullptr;
+    size_t got_ = 0;   // temp blocks only
 };
 
 int ensure_stage(rtb_scene *sc, size_t bytes) {
@@ -286,6 +298,20 @@ int scene_scratch(rtb_scene *sc, int which, size_t bytes, void **out) {
 }
 cudaStream_t scene_stream(rtb_scene *sc) { return sc->streams[0]; }
 }  // namespace rtb
+
+namespace {
+// queue cursors, streams, events of a new scene
+int finish_scene(rtb_scene *sc, const char *who) {
+    cudaError_t ce = cudaMalloc((void **) &sc->queue_heads, kQueueHeads * sizeof(unsigned));
+    for (auto &s : sc->streams) if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking);
+    for (auto &e : sc->ev) if (ce == cudaSuccess) ce = cudaEventCreate(&e);
+    if (ce != cudaSuccess) {
+        rtb::set_error(std::string(who) + ": " + cudaGetErrorString(ce));
+        return RTB_ERR_CUDA;
+    }
+    return RTB_OK;
+}
+}  // namespace
 
 extern "C" {
 
@@ -348,18 +374,226 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
     fill_bvh_scalars(L.bvh, sc->d.bvh, desc->n_tris);
     if (desc->n_lights > 0) fill_bvh_scalars(L.light_bvh, sc->d.light_bvh, desc->n_lights);
     sc->traversal_bytes = L.bvh.nodes.size() * sizeof(DNode) + L.bvh.tris.size() * sizeof(float4);
+    sc->n_big = L.bvh.big.size();
     sc->d.n_meshes = L.n_meshes;
     fill_scalars(desc, sc->d);
 
     // (failures from here on still go through fail(): the scene and its device arena are released)
-    cudaError_t ce = cudaMalloc((void **) &sc->queue_heads, kQueueHeads * sizeof(unsigned));
-    for (auto &s : sc->streams) if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking);
-    for (auto &e : sc->ev) if (ce == cudaSuccess) ce = cudaEventCreate(&e);
-    if (ce != cudaSuccess) {
-        rtb::set_error(std::string("rtb_scene_create: ") + cudaGetErrorString(ce));
+    if ((rc = finish_scene(sc, "rtb_scene_create")) != RTB_OK) return fail(rc);
+    *out = sc;
+    return RTB_OK;
+}
+
+// Device-side assembly (include/rtb.h, csrc/rtb_assemble.cuh): the raw views and the reference-order nodes are uploaded as
+// they are into a temporary block; two kernels write the scene's own buffers from them.
+int rtb_scene_create_raw(const rtb_scene_desc *desc, const rtb_raw_geometry *raw, int device, rtb_scene **out) {
+    if (!desc || !raw || !out) { rtb::set_error("rtb_scene_create_raw: null argument"); return RTB_ERR_INVALID; }
+    *out = nullptr;
+    const int ndev = rtb_device_count();
+    if (ndev <= 0) { rtb::set_error("no CUDA device available (this library has no CPU fallback)"); return RTB_ERR_NO_DEVICE; }
+    if (device < 0 || device >= ndev) { rtb::set_error("rtb_scene_create_raw: device index out of range"); return RTB_ERR_INVALID; }
+    auto invalid = [](const std::string &m) { rtb::set_error("rtb_scene_create_raw: " + m); return RTB_ERR_INVALID; };
+    if (!raw->meshes || raw->n_meshes == 0 || !raw->tri_source) return invalid("no raw meshes / tri_source");
+    if (desc->n_tris == 0 || desc->n_tris >= (1u << 28)) return invalid(desc->n_tris ? "too many triangles for the 28-bit leaf link" : "scene without nodes / triangles");
+
+    std::string err;
+    HostLayout L;
+    if (!build_layout_common(desc, L, err)) return invalid(err);
+    // ---- the views: validated, then merged into the byte ranges that are uploaded (interleaved views share their bytes)
+    struct Range { const uint8_t *b, *e; };
+    std::vector<Range> ranges;
+    std::vector<uint32_t> mesh_first(raw->n_meshes + 1, 0);
+    for (uint32_t m = 0; m < raw->n_meshes; ++m) {
+        const rtb_raw_mesh &r = raw->meshes[m];
+        if ((uint64_t) mesh_first[m] + r.n_tris >= (1ull << 32)) return invalid("too many raw triangles");
+        mesh_first[m + 1] = mesh_first[m] + r.n_tris;
+        if (r.n_tris == 0) continue;
+        if (r.mesh_id < 0 || r.mesh_id >= L.n_meshes) return invalid("mesh id out of range");
+        if (!r.position || r.n_vertices == 0) return invalid("raw mesh without positions");
+        if (r.normal_mode < RTB_NORMALS_TRANSFORM || r.normal_mode > RTB_NORMALS_FLAT || (r.normal_mode == RTB_NORMALS_VERBATIM && !r.normal))
+            return invalid("bad normal_mode");
+        auto view = [&](const void *p, int stride, size_t elem, size_t count) -> bool {
+            if (!p) return true;
+            if (stride < (int) elem || stride % 4 != 0 || ((uintptr_t) p & 3u)) return false;
+            ranges.push_back({(const uint8_t *) p, (const uint8_t *) p + (count - 1) * (size_t) stride + elem});
+            return true;
+        };
+        if (!view(r.position, r.position_stride, 12, r.n_vertices) || !view(r.normal, r.normal_stride, 12, r.n_vertices) ||
+            !view(r.tangent, r.tangent_stride, 16, r.n_vertices) || !view(r.texcoord, r.texcoord_stride, 8, r.n_vertices))
+            return invalid("vertex views must be 4-byte aligned with strides that are multiples of 4 (use rtb_scene_create for other files)");
+        if (r.indices) {
+            if ((r.index_bytes != 2 && r.index_bytes != 4) || r.index_stride < r.index_bytes || r.index_stride % r.index_bytes != 0 ||
+                ((uintptr_t) r.indices % (uintptr_t) r.index_bytes))
+                return invalid("index view: 2- or 4-byte indices, aligned");
+            ranges.push_back({(const uint8_t *) r.indices, (const uint8_t *) r.indices + ((size_t) r.n_tris * 3 - 1) * (size_t) r.index_stride + (size_t) r.index_bytes});
+        } else if ((uint64_t) r.n_tris * 3 > r.n_vertices) {
+            return invalid("[gltf check] vertex index out of range");
+        }
+    }
+    for (auto &g : ranges) g.b = (const uint8_t *) ((uintptr_t) g.b & ~(uintptr_t) 15);   // (stays inside the page of the first byte)
+    std::sort(ranges.begin(), ranges.end(), [](const Range &a, const Range &b) { return a.b < b.b; });
+    std::vector<Range> merged;
+    for (const Range &g : ranges) {
+        if (!merged.empty() && g.b <= merged.back().e + 64) merged.back().e = std::max(merged.back().e, g.e);
+        else merged.push_back(g);
+    }
+    // ---- nodes
+    const int32_t *root = desc->node_links;
+    const bool root_leaf = root[4] > 0;
+    if (!root_leaf && (desc->n_nodes & 1u) == 0) return invalid("nodes are not in the reference's order");
+    const uint32_t n_internal = root_leaf ? 0u : (desc->n_nodes - 1u) / 2u;
+    LeafLinker leaf;
+    big_leaf_slots(desc->n_nodes, desc->node_links, desc->n_tris, L.bvh.big, leaf.big_node, leaf.big_slot);
+    if (root_leaf && (root[3] < 0 || (uint64_t) root[3] + (uint64_t) root[4] > desc->n_tris)) return invalid("leaf range out of bounds");
+
+    RTB_CUDA(cudaSetDevice(device));
+    rtb_scene *sc = new rtb_scene();
+    sc->device = device;
+    std::memset(&sc->d, 0, sizeof(sc->d));
+    Uploader up, tmp;
+    auto fail = [&](int rc) { tmp.release_temp(sc); delete sc; return rc; };
+    int rc;
+    fill_lut(L.lut);
+    std::vector<DTexture> tex(desc->n_textures);
+    std::vector<const void *> tex_ptr(desc->n_textures, nullptr);
+    auto add = [&up](const auto &v, auto **dst) { up.add(v.data(), v.size() * sizeof(v[0]), (const void **) dst); };
+    const size_t nt = desc->n_tris;
+    up.add(nullptr, (size_t) n_internal * sizeof(DNode), (const void **) &sc->d.bvh.nodes);
+    up.add(nullptr, nt * kTriStride * sizeof(float4), (const void **) &sc->d.bvh.tris);
+    add(L.bvh.big, &sc->d.bvh.big_leaves);
+    up.add(nullptr, nt * 4 * sizeof(float4), (const void **) &sc->d.tri_shade);
+    if (L.any_normal_map) up.add(nullptr, nt * 3 * sizeof(float4), (const void **) &sc->d.tri_tan);
+    add(L.material, &sc->d.mesh_material);
+    add(L.normal_transform, &sc->d.mesh_normal_transform);
+    if (desc->n_lights > 0) {
+        add(L.light_bvh.nodes, &sc->d.light_bvh.nodes);
+        add(L.light_bvh.tris, &sc->d.light_bvh.tris);
+        add(L.light_bvh.big, &sc->d.light_bvh.big_leaves);
+        add(L.light_bvh.inv_area, &sc->d.light_inv_area);
+    }
+    add(L.lut, &sc->d.lut);
+    add(tex, &sc->d.textures);
+    for (uint32_t i = 0; i < desc->n_textures; ++i) {
+        const rtb_texture_desc &t = desc->textures[i];
+        up.add(t.rgba, (size_t) t.width * t.height * 4, &tex_ptr[i]);
+    }
+    if ((rc = up.alloc(sc)) != RTB_OK) return fail(rc);
+    for (uint32_t i = 0; i < desc->n_textures; ++i) tex[i] = {(const uchar4 *) tex_ptr[i], desc->textures[i].width, desc->textures[i].height};
+
+    // ---- the temporary block: raw bytes, reference-order nodes, tables, the two node frontiers
+    std::vector<DRawMesh> dmesh(raw->n_meshes);
+    std::vector<const void *> range_dev(merged.size(), nullptr);
+    const float *d_aabb = nullptr;
+    const int32_t *d_links = nullptr;
+    const uint32_t *d_source = nullptr, *d_first = nullptr, *d_big_node = nullptr, *d_big_slot = nullptr;
+    const DRawMesh *d_mesh = nullptr;
+    const NodeItem *d_items = nullptr;
+    const unsigned *d_words = nullptr;   // [0,1]: frontier sizes, [2]: error flag
+    for (size_t k = 0; k < merged.size(); ++k) tmp.add(merged[k].b, (size_t) (merged[k].e - merged[k].b), &range_dev[k]);
+    tmp.add(raw->tri_source, nt * sizeof(uint32_t), (const void **) &d_source);
+    tmp.add(mesh_first.data(), mesh_first.size() * sizeof(uint32_t), (const void **) &d_first);
+    tmp.add(dmesh.data(), dmesh.size() * sizeof(DRawMesh), (const void **) &d_mesh);
+    if (n_internal > 0) {
+        tmp.add(desc->node_aabb, (size_t) desc->n_nodes * 6 * sizeof(float), (const void **) &d_aabb);
+        tmp.add(desc->node_links, (size_t) desc->n_nodes * 5 * sizeof(int32_t), (const void **) &d_links);
+        tmp.add(leaf.big_node.data(), leaf.big_node.size() * sizeof(uint32_t), (const void **) &d_big_node);
+        tmp.add(leaf.big_slot.data(), leaf.big_slot.size() * sizeof(uint32_t), (const void **) &d_big_slot);
+        tmp.add(nullptr, (size_t) n_internal * 2 * sizeof(NodeItem), (const void **) &d_items);
+    }
+    tmp.add(nullptr, 256, (const void **) &d_words);
+    if ((rc = tmp.alloc(sc, true)) != RTB_OK) return fail(rc);
+    auto to_dev = [&](const void *p) -> const uint8_t * {
+        if (!p) return nullptr;
+        // the merged range that holds p: the last one starting at or before it
+        size_t lo = 0, hi = merged.size();
+        while (hi - lo > 1) {
+            const size_t mid = (lo + hi) / 2;
+            if (merged[mid].b <= (const uint8_t *) p) lo = mid; else hi = mid;
+        }
+        return (const uint8_t *) range_dev[lo] + ((const uint8_t *) p - merged[lo].b);
+    };
+    for (uint32_t m = 0; m < raw->n_meshes; ++m) {
+        const rtb_raw_mesh &r = raw->meshes[m];
+        DRawMesh &d = dmesh[m];
+        std::memset(&d, 0, sizeof(d));
+        if (r.n_tris == 0) continue;
+        d.idx = to_dev(r.indices); d.pos = to_dev(r.position); d.nrm = to_dev(r.normal); d.tan = to_dev(r.tangent); d.uv = to_dev(r.texcoord);
+        d.first_tri = mesh_first[m]; d.n_tris = r.n_tris; d.n_vertices = r.n_vertices;
+        d.index_bytes = r.index_bytes; d.idx_stride = r.index_stride;
+        d.pos_stride = r.position_stride; d.nrm_stride = r.normal_stride; d.tan_stride = r.tangent_stride; d.uv_stride = r.texcoord_stride;
+        d.normal_mode = r.normal_mode; d.flags = r.flags; d.mesh_id = r.mesh_id;
+        std::memcpy(d.transform, r.transform, sizeof(d.transform));
+        std::memcpy(d.normal_transform, &L.normal_transform[(size_t) r.mesh_id * 16], sizeof(d.normal_transform));
+    }
+    // (failures from here on still go through fail(): the scene, its arena and the temporary block are released)
+    if ((rc = finish_scene(sc, "rtb_scene_create_raw")) != RTB_OK) return fail(rc);
+    if ((rc = up.run(sc)) != RTB_OK) return fail(rc);
+    if ((rc = tmp.run(sc)) != RTB_OK) return fail(rc);
+    cudaStream_t st = sc->streams[0];
+    unsigned *words = const_cast<unsigned *>(d_words);
+    int *d_error = (int *) (words + 2);
+    cudaError_t ce = cudaMemsetAsync(words, 0, 256, st);
+    int levels = 0;
+    if (ce == cudaSuccess) {
+        launch_assemble_triangles(d_mesh, d_first, (int) raw->n_meshes, d_source, desc->n_tris, const_cast<float4 *>(sc->d.bvh.tris),
+                                  const_cast<float4 *>(sc->d.tri_shade), const_cast<float4 *>(sc->d.tri_tan), d_error, st);
+        const BigLeafIndex big{d_big_node, d_big_slot, (int) leaf.big_node.size()};
+        levels = launch_convert_nodes(desc->n_nodes, n_internal, desc->n_tris, d_aabb, d_links, big, const_cast<DNode *>(sc->d.bvh.nodes),
+                                      const_cast<NodeItem *>(d_items), words, d_error, st);
+        sc->launches = 0;
+    }
+    int flagged = 0;
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(&flagged, d_error, sizeof(int), cudaMemcpyDeviceToHost, st);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
+    if (ce == cudaSuccess) ce = cudaGetLastError();
+    if (ce != cudaSuccess || levels < 0) {
+        rtb::set_error(std::string("rtb_scene_create_raw: ") + (ce != cudaSuccess ? cudaGetErrorString(ce) : "node conversion failed"));
         return fail(RTB_ERR_CUDA);
     }
+    if (flagged != kAsmOk) { rtb::set_error(std::string("rtb_scene_create_raw: ") + assemble_error_text(flagged)); return fail(RTB_ERR_INVALID); }
+    if (levels > kMaxStack) {
+        rtb::set_error("rtb_scene_create_raw: BVH deeper than the traversal stack (" + std::to_string(levels) + " > " + std::to_string(kMaxStack) + ")");
+        return fail(RTB_ERR_INVALID);
+    }
+    tmp.release_temp(sc);
+    std::memcpy(sc->d.bvh.root_box, desc->node_aabb, 24);
+    sc->d.bvh.root_link = root_leaf ? leaf.link(0, root[3], root[4]) : 0;
+    sc->d.bvh.n_internal = (int) n_internal;
+    sc->d.bvh.n_tris = (int) desc->n_tris;
+    sc->d.bvh.max_depth = levels;
+    if (desc->n_lights > 0) fill_bvh_scalars(L.light_bvh, sc->d.light_bvh, desc->n_lights);
+    sc->traversal_bytes = (size_t) n_internal * sizeof(DNode) + nt * kTriStride * sizeof(float4);
+    sc->n_big = L.bvh.big.size();
+    sc->d.n_meshes = L.n_meshes;
+    fill_scalars(desc, sc->d);
     *out = sc;
+    return RTB_OK;
+}
+
+int rtb_scene_read_buffer(rtb_scene *scene, int which, void *dst, size_t *bytes) {
+    if (!scene || !bytes) { rtb::set_error("rtb_scene_read_buffer: null argument"); return RTB_ERR_INVALID; }
+    RTB_CUDA(cudaSetDevice(scene->device));
+    const DBvh &b = scene->d.bvh;
+    const void *src = nullptr;
+    size_t size = 0;
+    struct { float box[6]; int32_t v[4]; } scalars;
+    switch (which) {
+        case RTB_BUF_NODES: src = b.nodes; size = (size_t) b.n_internal * sizeof(DNode); break;
+        case RTB_BUF_TRIS: src = b.tris; size = (size_t) b.n_tris * kTriStride * sizeof(float4); break;
+        case RTB_BUF_SHADE: src = scene->d.tri_shade; size = (size_t) b.n_tris * 4 * sizeof(float4); break;
+        case RTB_BUF_TANGENTS: src = scene->d.tri_tan; size = scene->d.tri_tan ? (size_t) b.n_tris * 3 * sizeof(float4) : 0; break;
+        case RTB_BUF_BIG_LEAVES: src = b.big_leaves; size = scene->n_big * sizeof(int2); break;
+        case RTB_BUF_BVH_SCALARS:
+            std::memcpy(scalars.box, b.root_box, 24);
+            scalars.v[0] = b.root_link; scalars.v[1] = b.n_internal; scalars.v[2] = b.n_tris; scalars.v[3] = b.max_depth;
+            size = sizeof(scalars);
+            if (dst) std::memcpy(dst, &scalars, std::min(*bytes, size));
+            *bytes = size;
+            return RTB_OK;
+        default: rtb::set_error("rtb_scene_read_buffer: unknown buffer"); return RTB_ERR_INVALID;
+    }
+    if (dst && size && *bytes) RTB_CUDA(cudaMemcpy(dst, src, std::min(*bytes, size), cudaMemcpyDeviceToHost));
+    *bytes = size;
     return RTB_OK;
 }
 

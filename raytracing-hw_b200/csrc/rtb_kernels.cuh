@@ -64,4 +64,13 @@ int launch_render_wavefront(const DScene &sc, const RenderLaunch &p, void *state
                             std::vector<cudaEvent_t> *stage_events, WfStreams *aux);
 void launch_resolve(const float *d_accum, size_t n_pixels, int samples, uint8_t *d_rgb8, cudaStream_t stream);
 
+// device-side scene assembly (rtb_assemble.cu / rtb_assemble.cuh)
+struct DRawMesh;
+struct NodeItem;
+struct BigLeafIndex;
+void launch_assemble_triangles(const DRawMesh *d_meshes, const uint32_t *d_mesh_first, int n_meshes, const uint32_t *d_tri_source, uint32_t n_tris,
+                               float4 *d_tris, float4 *d_shade, float4 *d_tan, int *d_error, cudaStream_t stream);
+int launch_convert_nodes(uint32_t n_nodes, uint32_t n_internal, uint32_t n_tris, const float *d_aabb, const int32_t *d_links, const BigLeafIndex &big,
+                         DNode *d_nodes, NodeItem *d_items, unsigned *d_counts, int *d_error, cudaStream_t stream);
+
 }  // namespace rtb

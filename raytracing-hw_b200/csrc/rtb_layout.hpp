@@ -24,14 +24,32 @@ struct HostBvhOut {
     int max_depth = 0;
 };
 
-inline int make_leaf_link(HostBvhOut &o, int first, int count) {
-    if (count >= 1 && count <= 7) return kLeafFlag | (count << 28) | first;
-    // a leaf of more than 7 triangles: a run of table entries {first + 7k, count - 7k}.  The link names the first one
-    // (the whole leaf: what decode_leaf reads); the queue kernels take 7 triangles at a time and step along the run
-    const int index = (int) o.big.size();
-    for (int k = 0; 7 * k < count; ++k) o.big.push_back(make_int2(first + 7 * k, count - 7 * k));
-    return kLeafFlag | index;
+// Leaves of more than 7 triangles go through a table: a run of entries {first + 7k, count - 7k} per leaf (the link names
+// the first one -- the whole leaf: what decode_leaf reads; the queue kernels take 7 triangles at a time and step along
+// the run).  The runs are laid out in REFERENCE NODE ORDER, so that the host conversion below and the device-side one
+// (rtb_assemble.cuh) produce the same table: big_node[k] = node index of the k-th such leaf (ascending), big_slot[k] =
+// its first entry.
+inline void big_leaf_slots(uint32_t n_nodes, const int32_t *links, uint32_t n_tris, std::vector<int2> &big, std::vector<uint32_t> &big_node,
+                           std::vector<uint32_t> &big_slot) {
+    big.clear(); big_node.clear(); big_slot.clear();
+    for (uint32_t i = 0; i < n_nodes; ++i) {
+        const int first = links[(size_t) i * 5 + 3], count = links[(size_t) i * 5 + 4];
+        if (count <= 7 || (uint32_t) count > n_tris) continue;   // (a count beyond the array is rejected by the range check)
+        big_node.push_back(i);
+        big_slot.push_back((uint32_t) big.size());
+        for (int k = 0; 7 * k < count; ++k) big.push_back(make_int2(first + 7 * k, count - 7 * k));
+    }
 }
+
+struct LeafLinker {
+    std::vector<uint32_t> big_node, big_slot;
+    int link(uint32_t node, int first, int count) const {
+        if (count >= 1 && count <= 7) return kLeafFlag | (count << 28) | first;
+        const auto it = std::lower_bound(big_node.begin(), big_node.end(), node);
+        if (it == big_node.end() || *it != node) return kLeafFlag | (1 << 28);   // (only for a leaf the range check rejects)
+        return kLeafFlag | (int) big_slot[(size_t) (it - big_node.begin())];
+    }
+};
 
 // reference-order nodes (aabb6, links5) -> device layout.  Internal nodes are numbered in depth-first (left first)
 // order; triangle ids are untouched.
@@ -70,8 +88,10 @@ inline bool convert_bvh(uint32_t n_nodes, const float *aabb, const int32_t *link
         return true;
     };
     if (!check(0)) return false;
+    LeafLinker leaf;
+    big_leaf_slots(n_nodes, links, n_tris, o.big, leaf.big_node, leaf.big_slot);
     if (is_leaf(0)) {
-        o.root_link = make_leaf_link(o, links[3], links[4]);
+        o.root_link = leaf.link(0, links[3], links[4]);
         o.max_depth = 0;
         return true;
     }
@@ -95,8 +115,8 @@ inline bool convert_bvh(uint32_t n_nodes, const float *aabb, const int32_t *link
         int dev_r = -1, dev_l = -1;
         if (!is_leaf(L)) { dev_l = (int) o.nodes.size(); o.nodes.emplace_back(); }
         if (!is_leaf(R)) { dev_r = (int) o.nodes.size(); o.nodes.emplace_back(); }
-        link_l = is_leaf(L) ? make_leaf_link(o, links[(size_t) L * 5 + 3], links[(size_t) L * 5 + 4]) : dev_l;
-        link_r = is_leaf(R) ? make_leaf_link(o, links[(size_t) R * 5 + 3], links[(size_t) R * 5 + 4]) : dev_r;
+        link_l = is_leaf(L) ? leaf.link(L, links[(size_t) L * 5 + 3], links[(size_t) L * 5 + 4]) : dev_l;
+        link_r = is_leaf(R) ? leaf.link(R, links[(size_t) R * 5 + 3], links[(size_t) R * 5 + 4]) : dev_r;
         if (dev_r >= 0) stack.push_back({R, dev_r, it.depth + 1});
         if (dev_l >= 0) stack.push_back({L, dev_l, it.depth + 1});
         DNode nd;
@@ -135,11 +155,13 @@ struct HostLayout {
     std::vector<float4> material;           // DScene::mesh_material
     std::vector<double> normal_transform;   // DScene::mesh_normal_transform
     int n_meshes = 0;
+    bool any_normal_map = false;
     std::vector<float> lut;                 // DScene::lut
 };
 
-inline bool build_layout(const rtb_scene_desc *desc, HostLayout &L, std::string &err) {
-    if (!desc->node_aabb || !desc->node_links || !desc->tri_pos || desc->n_tris == 0 || desc->n_nodes == 0) {
+// everything but the scene's own triangles and nodes: constants, light BVH (small, host-assembled), materials, textures
+inline bool build_layout_common(const rtb_scene_desc *desc, HostLayout &L, std::string &err) {
+    if (!desc->node_aabb || !desc->node_links || desc->n_tris == 0 || desc->n_nodes == 0) {
         err = "scene without nodes / triangles";
         return false;
     }
@@ -147,7 +169,6 @@ inline bool build_layout(const rtb_scene_desc *desc, HostLayout &L, std::string 
         err = "ray_depth outside [0, " + std::to_string(kMaxRayDepth) + "]";
         return false;
     }
-    if (!convert_bvh(desc->n_nodes, desc->node_aabb, desc->node_links, desc->n_tris, desc->tri_pos, L.bvh, err)) return false;
     if (desc->n_lights > 0) {
         if (!desc->light_pos || !desc->light_node_aabb || !desc->light_node_links || desc->n_light_nodes == 0) {
             err = "light list without its BVH";
@@ -158,7 +179,6 @@ inline bool build_layout(const rtb_scene_desc *desc, HostLayout &L, std::string 
             return false;
         }
     }
-    const size_t nt = desc->n_tris;
     std::vector<float> mat;
     if (desc->n_meshes > 0 && desc->mesh_material && desc->mesh_normal_transform) {
         mat.assign(desc->mesh_material, desc->mesh_material + (size_t) desc->n_meshes * 16);
@@ -170,14 +190,14 @@ inline bool build_layout(const rtb_scene_desc *desc, HostLayout &L, std::string 
         L.normal_transform.assign(I, I + 16);
     }
     L.n_meshes = (int) (mat.size() / 16);
-    bool any_normal_map = false;
+    L.any_normal_map = false;
     for (int m = 0; m < L.n_meshes; ++m) {
         for (int k = 10; k < 14; ++k) {
             const int ti = (int) mat[(size_t) m * 16 + k];
             if (ti >= (int) desc->n_textures) { err = "texture index out of range"; return false; }
             if (ti < 0) mat[(size_t) m * 16 + k] = -1.f;
         }
-        any_normal_map = any_normal_map || mat[(size_t) m * 16 + 11] >= 0.f;
+        L.any_normal_map = L.any_normal_map || mat[(size_t) m * 16 + 11] >= 0.f;
     }
     for (uint32_t i = 0; i < desc->n_textures; ++i) {
         const rtb_texture_desc &t = desc->textures[i];
@@ -185,11 +205,19 @@ inline bool build_layout(const rtb_scene_desc *desc, HostLayout &L, std::string 
     }
     L.material.resize((size_t) L.n_meshes * 4);
     std::memcpy(L.material.data(), mat.data(), mat.size() * sizeof(float));
+    return true;
+}
+
+inline bool build_layout(const rtb_scene_desc *desc, HostLayout &L, std::string &err) {
+    if (!desc->tri_pos) { err = "scene without nodes / triangles"; return false; }
+    if (!build_layout_common(desc, L, err)) return false;
+    if (!convert_bvh(desc->n_nodes, desc->node_aabb, desc->node_links, desc->n_tris, desc->tri_pos, L.bvh, err)) return false;
+    const size_t nt = desc->n_tris;
     if (desc->tri_mesh)
         for (size_t i = 0; i < nt; ++i)
             if (desc->tri_mesh[i] < 0 || desc->tri_mesh[i] >= L.n_meshes) { err = "mesh id out of range"; return false; }
     pack_shade(nt, desc->tri_nrm, desc->tri_uv, desc->tri_mesh, L.shade);
-    if (any_normal_map) {
+    if (L.any_normal_map) {
         if (!desc->tri_tan) { err = "normal-mapped material without tangents"; return false; }
         L.tan.resize(nt * 3);
         std::memcpy(L.tan.data(), desc->tri_tan, nt * 12 * sizeof(float));

@@ -184,6 +184,7 @@ void HostTriangles::permute(const std::vector<uint32_t> &order) {
     const size_t n = order.size();
     auto apply = [&](auto &vec, size_t stride) {
         using T = typename std::remove_reference<decltype(vec)>::type;
+        if (vec.empty()) return;   // (an attribute array that has not been assembled)
         T out(n * stride);
 #pragma omp parallel for schedule(static)
         for (size_t i = 0; i < n; ++i)
@@ -195,6 +196,7 @@ void HostTriangles::permute(const std::vector<uint32_t> &order) {
     apply(tan, 12);
     apply(uv, 6);
     apply(mesh, 1);
+    apply(source, 1);
 }
 
 void build_bvh(HostTriangles &tris, HostBvh &out, int threads) {

@@ -466,61 +466,135 @@ void load_gltf(const std::string &filename, int width, int height, int samples, 
             const size_t ntri = idx.count / 3;
             const size_t base = n_tris_total;
             n_tris_total += ntri;
-            scene.tris.resize(n_tris_total);
             const bool nv = nrm.ptr != nullptr, tv = uv.ptr != nullptr, gv = tan.ptr != nullptr;
+            RawMesh rm;
+            rm.n_tris = ntri;
+            rm.first_tri = base;
+            rm.idx = idx.ptr;
+            rm.index_bytes = idx.component_type == kU16 ? 2 : 4;
+            rm.idx_stride = idx.stride;
+            rm.pos = pos.ptr; rm.pos_stride = pos.stride;
+            rm.nrm = nrm.ptr; rm.nrm_stride = nrm.stride;
+            rm.tan = tan.ptr; rm.tan_stride = tan.stride;
+            rm.uv = uv.ptr; rm.uv_stride = uv.stride;
+            rm.n_vertices = pos.count;
+            if (nv) rm.n_vertices = std::min(rm.n_vertices, nrm.count);
+            if (tv) rm.n_vertices = std::min(rm.n_vertices, uv.count);
+            if (gv) rm.n_vertices = std::min(rm.n_vertices, tan.count);
+            rm.normal_mode = 0;   // RTB_NORMALS_TRANSFORM
+            rm.mesh_id = mesh_id;
+            std::memcpy(rm.transform, transform.d, sizeof(rm.transform));
+            std::memcpy(rm.normal_transform, normal_transform.d, sizeof(rm.normal_transform));
+            scene.tris.resize_core(n_tris_total);
+            // positions only: what the BVH build needs.  Normals, tangents and texcoords are assembled from the same views
+            // where they are consumed: on the GPU (rtb_scene_create_raw), or by HostScene::assemble_attributes.
             bool tangent_warned = false;
             for (size_t i = 0; i < ntri; ++i) {
-                size_t index[3];
-                for (int v = 0; v < 3; ++v) {
-                    if (idx.component_type == kU16) {
-                        uint16_t x;
-                        std::memcpy(&x, idx.at(i * 3 + (size_t) v), 2);
-                        index[v] = x;
-                    } else {
-                        uint32_t x;
-                        std::memcpy(&x, idx.at(i * 3 + (size_t) v), 4);
-                        index[v] = x;
-                    }
-                }
                 for (int v = 0; v < 3; ++v)   // (the reference indexes the raw buffers unchecked: scene_parser.cpp:306-343)
-                    if (index[v] >= pos.count || (nv && index[v] >= nrm.count) || (tv && index[v] >= uv.count) || (gv && index[v] >= tan.count))
-                        throw std::runtime_error("[gltf check] vertex index out of range");
+                    if (rm.vertex(i, v) >= rm.n_vertices) throw std::runtime_error("[gltf check] vertex index out of range");
                 const size_t t = base + i;
-                float P[3][4];
-                for (int v = 0; v < 3; ++v) {
-                    float in[4];
-                    std::memcpy(in, pos.at(index[v]), 12);
-                    in[3] = 1.f;
-                    mul_vec4(transform, in, P[v]);
-                }
-                float *o = &scene.tris.pos[t * 9];
-                for (int k = 0; k < 3; ++k) {
-                    o[k] = P[0][k];
-                    o[3 + k] = P[1][k] + (-P[0][k]);   // operator-(a,b) = a + (-b) (vector.h:326-328)
-                    o[6 + k] = P[2][k] + (-P[0][k]);
-                }
-                for (int v = 0; v < 3; ++v) {
-                    float in[4] = {0.f, 0.f, 1.f, 0.f};
-                    if (nv) std::memcpy(in, nrm.at(index[v]), 12);
-                    in[3] = 0.f;
-                    float res[4];
-                    mul_vec4(normal_transform, in, res);
-                    normalize3(res);
-                    for (int k = 0; k < 3; ++k) scene.tris.nrm[t * 9 + (size_t) v * 3 + k] = res[k];
-                }
-                if (tv)
-                    for (int v = 0; v < 3; ++v) std::memcpy(&scene.tris.uv[t * 6 + (size_t) v * 2], uv.at(index[v]), 8);
-                if (gv) {
-                    for (int v = 0; v < 3; ++v) std::memcpy(&scene.tris.tan[t * 12 + (size_t) v * 4], tan.at(index[v]), 16);
-                    const float side = scene.tris.tan[t * 12 + 3];
-                    if ((scene.tris.tan[t * 12 + 7] != side || scene.tris.tan[t * 12 + 11] != side) && !tangent_warned) {
+                assemble_triangle(rm, i, &scene.tris.pos[t * 9], nullptr, nullptr, nullptr);
+                if (gv && !tangent_warned) {
+                    float w[3];
+                    for (int v = 0; v < 3; ++v) std::memcpy(&w[v], tan.at(rm.vertex(i, v)) + 12, 4);
+                    if (w[1] != w[0] || w[2] != w[0]) {
                         std::cout << "Warning: tangent.w values differ within triangle" << std::endl;
                         tangent_warned = true;   // the reference prints this per triangle; once per primitive here
                     }
                 }
                 scene.tris.mesh[t] = mesh_id;
+                scene.tris.source[t] = (uint32_t) t;
+            }
+            scene.raw_meshes.push_back(rm);
+        }
+    }
+    scene.raw_buffers = std::move(buffers);   // (moving a vector keeps its storage: the views stay valid)
+}
+
+size_t RawMesh::vertex(size_t tri, int v) const {
+    const size_t k = tri * 3 + (size_t) v;
+    if (!idx) return k;
+    if (index_bytes == 2) {
+        uint16_t x;
+        std::memcpy(&x, idx + k * idx_stride, 2);
+        return x;
+    }
+    uint32_t x;
+    std::memcpy(&x, idx + k * idx_stride, 4);
+    return x;
+}
+
+void assemble_triangle(const RawMesh &m, size_t tri, float *pos9, float *nrm9, float *tan12, float *uv6) {
+    size_t index[3];
+    for (int v = 0; v < 3; ++v) index[v] = m.vertex(tri, v);
+    Mat4d T, N;
+    T.empty = N.empty = false;
+    std::memcpy(T.d, m.transform, sizeof(T.d));
+    std::memcpy(N.d, m.normal_transform, sizeof(N.d));
+    float U[3] = {0.f, 0.f, 0.f}, V[3] = {0.f, 0.f, 0.f};
+    if (pos9 || (nrm9 && m.normal_mode == 2)) {
+        float P[3][4];
+        for (int v = 0; v < 3; ++v) {
+            float in[4];
+            std::memcpy(in, m.pos + index[v] * m.pos_stride, 12);
+            in[3] = 1.f;
+            if (m.transform_positions) mul_vec4(T, in, P[v]);
+            else std::memcpy(P[v], in, 16);
+        }
+        for (int k = 0; k < 3; ++k) {
+            U[k] = P[1][k] + (-P[0][k]);   // operator-(a,b) = a + (-b) (vector.h:326-328)
+            V[k] = P[2][k] + (-P[0][k]);
+        }
+        if (pos9)
+            for (int k = 0; k < 3; ++k) {
+                pos9[k] = P[0][k];
+                pos9[3 + k] = U[k];
+                pos9[6 + k] = V[k];
+            }
+    }
+    if (nrm9) {
+        if (m.normal_mode == 2) {   // RTB_NORMALS_FLAT: normal(cross(U, V)) (vector.h:169-174, 372-378)
+            float c[3] = {U[1] * V[2] - V[1] * U[2], U[2] * V[0] - V[2] * U[0], U[0] * V[1] - V[0] * U[1]};
+            normalize3(c);
+            for (int v = 0; v < 3; ++v)
+                for (int k = 0; k < 3; ++k) nrm9[v * 3 + k] = c[k];
+        } else if (m.normal_mode == 1) {   // RTB_NORMALS_VERBATIM
+            for (int v = 0; v < 3; ++v) std::memcpy(nrm9 + v * 3, m.nrm + index[v] * m.nrm_stride, 12);
+        } else {
+            for (int v = 0; v < 3; ++v) {
+                float in[4] = {0.f, 0.f, 1.f, 0.f};
+                if (m.nrm) std::memcpy(in, m.nrm + index[v] * m.nrm_stride, 12);
+                in[3] = 0.f;
+                float res[4];
+                mul_vec4(N, in, res);
+                normalize3(res);
+                for (int k = 0; k < 3; ++k) nrm9[v * 3 + k] = res[k];
             }
         }
+    }
+    if (uv6) {
+        if (m.uv) for (int v = 0; v < 3; ++v) std::memcpy(uv6 + v * 2, m.uv + index[v] * m.uv_stride, 8);
+        else std::memset(uv6, 0, 24);
+    }
+    if (tan12) {
+        if (m.tan) for (int v = 0; v < 3; ++v) std::memcpy(tan12 + v * 4, m.tan + index[v] * m.tan_stride, 16);
+        else std::memset(tan12, 0, 48);
+    }
+}
+
+void HostScene::assemble_attributes() {
+    const size_t n = tris.size();
+    if (tris.nrm.size() == n * 9 && tris.uv.size() == n * 6 && tris.tan.size() == n * 12) return;
+    tris.nrm.assign(n * 9, 0.f);
+    tris.tan.assign(n * 12, 0.f);
+    tris.uv.assign(n * 6, 0.f);
+    std::vector<size_t> first(raw_meshes.size() + 1, 0);
+    for (size_t m = 0; m < raw_meshes.size(); ++m) first[m + 1] = first[m] + raw_meshes[m].n_tris;
+#pragma omp parallel for schedule(static)
+    for (long long i = 0; i < (long long) n; ++i) {
+        const size_t src = tris.source[(size_t) i];
+        const size_t m = (size_t) (std::upper_bound(first.begin(), first.end(), src) - first.begin()) - 1;
+        assemble_triangle(raw_meshes[m], src - first[m], nullptr, &tris.nrm[(size_t) i * 9], &tris.tan[(size_t) i * 12], &tris.uv[(size_t) i * 6]);
     }
 }
 

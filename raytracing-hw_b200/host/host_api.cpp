@@ -2,6 +2,7 @@
 #include "../../include/rtb.h"
 #include "host_scene.h"
 
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <fstream>
@@ -10,6 +11,7 @@
 struct rtb_host_scene {
     rtb::HostScene s;
     std::vector<rtb_texture_desc> tex_desc;
+    std::vector<rtb_raw_mesh> raw_desc;
 };
 
 namespace rtb {
@@ -49,27 +51,32 @@ int rtb_host_scene_from_triangles(const float *verts9, const float *nrm9, size_t
     rtb_host_scene *hs = new rtb_host_scene();
     rtb::HostScene &s = hs->s;
     try {
-        s.tris.resize(n);
-        for (size_t i = 0; i < n; ++i) {
-            const float *v = verts9 + i * 9;
-            float *o = &s.tris.pos[i * 9];
-            for (int k = 0; k < 3; ++k) {
-                o[k] = v[k];
-                o[3 + k] = v[3 + k] + (-v[k]);
-                o[6 + k] = v[6 + k] + (-v[k]);
-            }
-            if (nrm9) {
-                std::memcpy(&s.tris.nrm[i * 9], nrm9 + i * 9, 36);
-            } else {   // normal(cross(U, V)) (vector.h:169-174, 372-378)
-                const float *U = o + 3, *V = o + 6;
-                float c[3] = {U[1] * V[2] - V[1] * U[2], U[2] * V[0] - V[2] * U[0], U[0] * V[1] - V[0] * U[1]};
-                float mod = 0.f;
-                for (int k = 0; k < 3; ++k) mod += c[k] * c[k];
-                mod = 1.f / std::sqrt(mod);
-                for (int v3 = 0; v3 < 3; ++v3)
-                    for (int k = 0; k < 3; ++k) s.tris.nrm[i * 9 + v3 * 3 + k] = c[k] * mod;
-            }
-            s.tris.mesh[i] = (i >= emissive_from) ? 1 : 0;
+        // the caller's arrays are the "file": kept as raw views (two meshes: plain / emissive), positions assembled here
+        // for the BVH build, normals where they are consumed (HostScene::assemble_attributes / the GPU)
+        s.raw_buffers.resize(nrm9 ? 2 : 1);
+        s.raw_buffers[0].assign((const uint8_t *) verts9, (const uint8_t *) verts9 + n * 36);
+        if (nrm9) s.raw_buffers[1].assign((const uint8_t *) nrm9, (const uint8_t *) nrm9 + n * 36);
+        const size_t cut = std::min(emissive_from, n);
+        for (int part = 0; part < 2; ++part) {
+            rtb::RawMesh rm;
+            rm.first_tri = part == 0 ? 0 : cut;
+            rm.n_tris = part == 0 ? cut : n - cut;
+            rm.n_vertices = rm.n_tris * 3;
+            rm.pos = s.raw_buffers[0].data() + rm.first_tri * 36;
+            rm.pos_stride = 12;
+            if (nrm9) { rm.nrm = s.raw_buffers[1].data() + rm.first_tri * 36; rm.nrm_stride = 12; }
+            rm.normal_mode = nrm9 ? RTB_NORMALS_VERBATIM : RTB_NORMALS_FLAT;
+            rm.transform_positions = false;
+            rm.mesh_id = part;
+            s.raw_meshes.push_back(rm);
+        }
+        s.tris.resize_core(n);
+#pragma omp parallel for schedule(static)
+        for (long long i = 0; i < (long long) n; ++i) {
+            const int part = (size_t) i >= cut ? 1 : 0;
+            rtb::assemble_triangle(s.raw_meshes[(size_t) part], (size_t) i - s.raw_meshes[(size_t) part].first_tri, &s.tris.pos[(size_t) i * 9], nullptr, nullptr, nullptr);
+            s.tris.mesh[(size_t) i] = part;
+            s.tris.source[(size_t) i] = (uint32_t) i;
         }
         const float m0[16] = {1.f, 1.f, 1.f, 1.f, 1.f, 0.f, 0.f, 0.f, 0.f, 1.f, -1.f, -1.f, -1.f, -1.f, 0.f, 0.f};
         float m1[16];
@@ -96,12 +103,28 @@ int rtb_host_scene_from_triangles(const float *verts9, const float *nrm9, size_t
     return RTB_OK;
 }
 
+namespace {
+void fill_desc(rtb_host_scene *hs, rtb_scene_desc *d, bool attributes);
+}
+
 int rtb_host_scene_desc(const rtb_host_scene *hs_c, rtb_scene_desc *d) {
     if (!hs_c || !d) {
         rtb::set_error("rtb_host_scene_desc: invalid argument");
         return RTB_ERR_INVALID;
     }
     rtb_host_scene *hs = const_cast<rtb_host_scene *>(hs_c);
+    try {
+        hs->s.assemble_attributes();   // the flat description carries host-assembled normals / tangents / texcoords
+    } catch (const std::exception &e) {
+        rtb::set_error(e.what());
+        return RTB_ERR_INVALID;
+    }
+    fill_desc(hs, d, true);
+    return RTB_OK;
+}
+
+namespace {
+void fill_desc(rtb_host_scene *hs, rtb_scene_desc *d, bool attributes) {
     const rtb::HostScene &s = hs->s;
     std::memset(d, 0, sizeof(*d));
     d->n_nodes = (uint32_t) s.bvh.size();
@@ -109,9 +132,9 @@ int rtb_host_scene_desc(const rtb_host_scene *hs_c, rtb_scene_desc *d) {
     d->node_links = s.bvh.links.data();
     d->n_tris = (uint32_t) s.tris.size();
     d->tri_pos = s.tris.pos.data();
-    d->tri_nrm = s.tris.nrm.data();
-    d->tri_tan = s.tris.tan.data();
-    d->tri_uv = s.tris.uv.data();
+    d->tri_nrm = attributes ? s.tris.nrm.data() : nullptr;
+    d->tri_tan = attributes ? s.tris.tan.data() : nullptr;
+    d->tri_uv = attributes ? s.tris.uv.data() : nullptr;
     d->tri_mesh = s.tris.mesh.data();
     d->n_meshes = (uint32_t) s.n_meshes();
     d->mesh_material = s.mesh_material.data();
@@ -133,6 +156,39 @@ int rtb_host_scene_desc(const rtb_host_scene *hs_c, rtb_scene_desc *d) {
     d->ray_depth = s.ray_depth;
     d->max_distance = s.max_distance;
     d->bg_color[0] = d->bg_color[1] = d->bg_color[2] = 0.f;
+}
+}  // namespace
+
+int rtb_host_scene_raw_geometry(const rtb_host_scene *hs_c, rtb_scene_desc *desc, rtb_raw_geometry *raw) {
+    if (!hs_c || !raw) {
+        rtb::set_error("rtb_host_scene_raw_geometry: invalid argument");
+        return RTB_ERR_INVALID;
+    }
+    rtb_host_scene *hs = const_cast<rtb_host_scene *>(hs_c);
+    const rtb::HostScene &s = hs->s;
+    if (desc) fill_desc(hs, desc, false);
+    hs->raw_desc.clear();
+    for (const rtb::RawMesh &m : s.raw_meshes) {
+        rtb_raw_mesh r;
+        std::memset(&r, 0, sizeof(r));
+        r.n_tris = (uint32_t) m.n_tris;
+        r.n_vertices = (uint32_t) m.n_vertices;
+        r.indices = m.idx;
+        r.index_bytes = m.idx ? m.index_bytes : 0;
+        r.index_stride = (int32_t) m.idx_stride;
+        r.position = m.pos; r.position_stride = (int32_t) m.pos_stride;
+        r.normal = m.nrm; r.normal_stride = (int32_t) m.nrm_stride;
+        r.tangent = m.tan; r.tangent_stride = (int32_t) m.tan_stride;
+        r.texcoord = m.uv; r.texcoord_stride = (int32_t) m.uv_stride;
+        r.normal_mode = m.normal_mode;
+        r.flags = m.transform_positions ? 0 : RTB_RAW_WORLD_POSITIONS;
+        r.mesh_id = m.mesh_id;
+        std::memcpy(r.transform, m.transform, sizeof(r.transform));
+        hs->raw_desc.push_back(r);
+    }
+    raw->n_meshes = (uint32_t) hs->raw_desc.size();
+    raw->meshes = hs->raw_desc.data();
+    raw->tri_source = s.tris.source.data();
     return RTB_OK;
 }
 

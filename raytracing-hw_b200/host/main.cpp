@@ -118,14 +118,21 @@ int main(int argc, char *argv[]) {
         for (int i = 0; i < 5; ++i) std::cout << "\t" << i << ": " << counts[i] << std::endl;
         std::cout << "At most " << max_leaf << " objects in single node." << std::endl;
     }
+    // the triangles are assembled on the GPU from the file's own views (rtb_scene_create_raw); RT_ASSEMBLE=host: the
+    // host assembles them as the reference does while parsing (scene_parser.cpp:280-345) and uploads the result
     rtb_scene_desc desc;
-    check(rtb_host_scene_desc(hs, &desc), "desc");
+    rtb_raw_geometry raw;
+    const char *asm_env = std::getenv("RT_ASSEMBLE");
+    const bool host_assembly = asm_env && std::strcmp(asm_env, "host") == 0;
+    if (host_assembly) check(rtb_host_scene_desc(hs, &desc), "desc");
+    else check(rtb_host_scene_raw_geometry(hs, &desc, &raw), "desc");
 
     int ndev = rtb_device_count();
     if (ndev <= 0) throw std::runtime_error("no CUDA device available (this build has no CPU fallback)");
     if (const char *e = std::getenv("RT_GPUS")) ndev = std::max(1, std::min(ndev, std::atoi(e)));
     std::vector<rtb_scene *> scenes((size_t) ndev, nullptr);
-    for (int d = 0; d < ndev; ++d) check(rtb_scene_create(&desc, d, &scenes[(size_t) d]), "upload");
+    for (int d = 0; d < ndev; ++d)
+        check(host_assembly ? rtb_scene_create(&desc, d, &scenes[(size_t) d]) : rtb_scene_create_raw(&desc, &raw, d, &scenes[(size_t) d]), "upload");
     std::cout << "Scene loaded: " << std::setprecision(2) << seconds_since(t_all) << " seconds." << std::endl;
 
     std::cout << std::setprecision(6) << "Rendering scene." << std::endl;

@@ -119,6 +119,8 @@ def devsim():
         L.devsim_render_wavefront.argtypes = [C.POINTER(rtb.SceneDesc), C.POINTER(rtb.RenderParams), vp, vp, vp]
         L.devsim_render_wavefront_resume.argtypes = [C.POINTER(rtb.SceneDesc), C.POINTER(rtb.RenderParams), vp, vp, vp, vp]
         L.devsim_trace_path.argtypes = [C.POINTER(rtb.SceneDesc), vp, vp, C.c_uint, vp, C.POINTER(C.c_uint)]
+        L.devsim_layout.argtypes = [C.POINTER(rtb.SceneDesc), vp, vp, vp, vp, vp, C.c_int, vp]
+        L.devsim_assemble.argtypes = [C.POINTER(rtb.SceneDesc), C.POINTER(rtb.RawGeometry), vp, vp, vp, vp, vp, C.c_int, vp]
         _devsim = L
     return _devsim
 
@@ -202,6 +204,38 @@ def devsim_trace_path(hs, origin, direction, seed):
     after = C.c_uint()
     assert devsim().devsim_trace_path(C.byref(hs.desc), _p(o), _p(d), seed, _p(rgb), C.byref(after)) == 0
     return rgb, after.value
+
+
+def _layout_buffers(n_tris, n_nodes):
+    return dict(tris=np.zeros((n_tris, 16), np.float32), shade=np.zeros((n_tris, 16), np.float32), tan=np.zeros((n_tris, 12), np.float32),
+                nodes=np.zeros((max(0, (n_nodes - 1) // 2), 64), np.uint8), big=np.zeros((max(4096, n_tris), 2), np.int32), scalars=np.zeros(5, np.int32))
+
+
+def _trim(b):
+    b["nodes"] = b["nodes"][:b["scalars"][1]]
+    b["big"] = b["big"][:b["scalars"][3]]
+    if not b["scalars"][4]:
+        b["tan"] = b["tan"][:0]
+    return b
+
+
+def devsim_layout(desc):
+    """the device buffers rtb_scene_create builds on the host from the flat, host-assembled description"""
+    b = _layout_buffers(desc.n_tris, desc.n_nodes)
+    rc = devsim().devsim_layout(C.byref(desc), _p(b["tris"]), _p(b["shade"]), _p(b["tan"]), _p(b["nodes"]), _p(b["big"]), len(b["big"]), _p(b["scalars"]))
+    assert rc == 0, devsim().devsim_last_error()
+    return _trim(b)
+
+
+def devsim_assemble(desc, raw):
+    """the same buffers from the raw views: rtb_assemble.cuh's per-triangle / per-node functions run on the host.
+    Returns (buffers, None) or (None, error text)"""
+    b = _layout_buffers(desc.n_tris, desc.n_nodes)
+    rc = devsim().devsim_assemble(C.byref(desc), C.byref(raw), _p(b["tris"]), _p(b["shade"]), _p(b["tan"]), _p(b["nodes"]), _p(b["big"]), len(b["big"]),
+                                  _p(b["scalars"]))
+    if rc != 0:
+        return None, devsim().devsim_last_error().decode()
+    return _trim(b), None
 
 
 def twin_bvh(hs, lights=False):

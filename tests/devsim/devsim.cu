@@ -5,6 +5,7 @@
 #include "../../raytracing-hw_b200/csrc/rtb_layout.hpp"
 #include "../../raytracing-hw_b200/csrc/rtb_wavefront.cuh"
 #include "../../raytracing-hw_b200/csrc/rtb_trace.cuh"
+#include "../../raytracing-hw_b200/csrc/rtb_assemble.cuh"
 
 #include <omp.h>
 
@@ -285,6 +286,87 @@ int devsim_trace_path(const rtb_scene_desc *desc, const float *o3, const float *
     const V3 c = trace_path<0, false>(s.d, r, g, &pc);
     rgb3[0] = c.x; rgb3[1] = c.y; rgb3[2] = c.z;
     *engine_after = g.x;
+    return 0;
+}
+
+// ---- scene assembly.  devsim_layout: the buffers rtb_scene_create uploads (rtb_layout.hpp, from the host-assembled arrays);
+// devsim_assemble: the buffers rtb_scene_create_raw's kernels write, produced by running rtb_assemble.cuh's per-triangle /
+// per-node functions on the host over the caller's raw views.  Buffers are caller-allocated: tris n x 16 floats, shade
+// n x 16 floats, tan n x 12 floats (or null), nodes (n_nodes - 1) / 2 x 64 bytes, big `big_cap` int2; scalars =
+// {root_link, n_internal, max_depth, n_big, has_tan}.
+int devsim_layout(const rtb_scene_desc *desc, float *tris, float *shade, float *tan, void *nodes, int *big, int big_cap, int *scalars) {
+    HostLayout L;
+    if (!build_layout(desc, L, g_err)) return 1;
+    std::memcpy(tris, L.bvh.tris.data(), L.bvh.tris.size() * sizeof(float4));
+    std::memcpy(shade, L.shade.data(), L.shade.size() * sizeof(float4));
+    if (tan && !L.tan.empty()) std::memcpy(tan, L.tan.data(), L.tan.size() * sizeof(float4));
+    std::memcpy(nodes, L.bvh.nodes.data(), L.bvh.nodes.size() * sizeof(DNode));
+    if ((int) L.bvh.big.size() > big_cap) { g_err = "big-leaf table larger than the caller's buffer"; return 1; }
+    std::memcpy(big, L.bvh.big.data(), L.bvh.big.size() * sizeof(int2));
+    scalars[0] = L.bvh.root_link; scalars[1] = (int) L.bvh.nodes.size(); scalars[2] = L.bvh.max_depth; scalars[3] = (int) L.bvh.big.size();
+    scalars[4] = L.tan.empty() ? 0 : 1;
+    return 0;
+}
+
+int devsim_assemble(const rtb_scene_desc *desc, const rtb_raw_geometry *raw, float *tris, float *shade, float *tan, void *nodes, int *big, int big_cap,
+                    int *scalars) {
+    HostLayout L;
+    if (!build_layout_common(desc, L, g_err)) return 1;
+    std::vector<DRawMesh> mesh(raw->n_meshes);
+    std::vector<uint32_t> first(raw->n_meshes + 1, 0);
+    for (uint32_t m = 0; m < raw->n_meshes; ++m) {
+        const rtb_raw_mesh &r = raw->meshes[m];
+        DRawMesh &d = mesh[m];
+        std::memset(&d, 0, sizeof(d));
+        first[m + 1] = first[m] + r.n_tris;
+        if (r.n_tris == 0) continue;
+        d.idx = (const uint8_t *) r.indices; d.pos = (const uint8_t *) r.position; d.nrm = (const uint8_t *) r.normal;
+        d.tan = (const uint8_t *) r.tangent; d.uv = (const uint8_t *) r.texcoord;
+        d.first_tri = first[m]; d.n_tris = r.n_tris; d.n_vertices = r.n_vertices;
+        d.index_bytes = r.index_bytes; d.idx_stride = r.index_stride;
+        d.pos_stride = r.position_stride; d.nrm_stride = r.normal_stride; d.tan_stride = r.tangent_stride; d.uv_stride = r.texcoord_stride;
+        d.normal_mode = r.normal_mode; d.flags = r.flags; d.mesh_id = r.mesh_id;
+        std::memcpy(d.transform, r.transform, sizeof(d.transform));
+        std::memcpy(d.normal_transform, &L.normal_transform[(size_t) r.mesh_id * 16], sizeof(d.normal_transform));
+    }
+    int error = kAsmOk;
+    const bool want_tan = L.any_normal_map && tan;
+    for (uint32_t i = 0; i < desc->n_tris; ++i) {
+        const uint32_t src = raw->tri_source[i];
+        if (src >= first[raw->n_meshes]) { error = kAsmSource; break; }
+        const int m = mesh_of_source(first.data(), (int) raw->n_meshes, src);
+        const int e = assemble_triangle_records(mesh[(size_t) m], src - first[(size_t) m], (float4 *) tris + (size_t) i * kTriStride, (float4 *) shade + (size_t) i * 4,
+                                                want_tan ? (float4 *) tan + (size_t) i * 3 : nullptr);
+        if (e != kAsmOk && error == kAsmOk) error = e;
+    }
+    LeafLinker leaf;
+    big_leaf_slots(desc->n_nodes, desc->node_links, desc->n_tris, L.bvh.big, leaf.big_node, leaf.big_slot);
+    if ((int) L.bvh.big.size() > big_cap) { g_err = "big-leaf table larger than the caller's buffer"; return 1; }
+    std::memcpy(big, L.bvh.big.data(), L.bvh.big.size() * sizeof(int2));
+    const int32_t *root = desc->node_links;
+    const bool root_leaf = root[4] > 0;
+    const uint32_t n_internal = root_leaf ? 0u : (desc->n_nodes - 1u) / 2u;
+    int levels = 0;
+    if (!root_leaf) {
+        const BigLeafIndex bigx{leaf.big_node.data(), leaf.big_slot.data(), (int) leaf.big_node.size()};
+        std::vector<NodeItem> cur{NodeItem{0u, 0u, 1u, desc->n_nodes}}, next;
+        while (!cur.empty() && error == kAsmOk) {
+            ++levels;
+            next.clear();
+            for (const NodeItem &it : cur) {
+                NodeItem kids[2];
+                int nk = 0;
+                const int e = convert_node(it, desc->n_nodes, n_internal, desc->n_tris, desc->node_aabb, desc->node_links, bigx, (DNode *) nodes, kids, &nk);
+                if (e != kAsmOk) { error = e; break; }
+                for (int k = 0; k < nk; ++k) next.push_back(kids[k]);
+                if (next.size() > n_internal) { error = kAsmNodeOrder; break; }
+            }
+            cur.swap(next);
+        }
+    }
+    if (error != kAsmOk) { g_err = assemble_error_text(error); return 2; }
+    scalars[0] = root_leaf ? leaf.link(0, root[3], root[4]) : 0; scalars[1] = (int) n_internal; scalars[2] = levels; scalars[3] = (int) L.bvh.big.size();
+    scalars[4] = want_tan ? 1 : 0;
     return 0;
 }
 

@@ -2,7 +2,7 @@
 # The one GPU-box runner (replaces the per-experiment scripts of round 1):  tools/gpu_run.sh <tag> <stage> [<stage> ...]
 # Every stage writes gpurun_out/<tag>_<stage>.{log,json,csv}; nothing here is timed under a profiler except the ncu stages.
 # Stages:  tests | tests_quick | smoke | bench | bench_short | bench_s7_4 | bench_soup10m | closest_hit | launches | ncu_trace |
-#          ncu_shade | ncu_soup10m | ncu_s7_4 | variants (needs VARIANTS="a.so b.so", SPP) | multi (needs NGPU) | scale (needs NGPU)
+#          ncu_shade | ncu_soup10m | ncu_s7_4 | ncu_frame | variants (needs VARIANTS="a.so b.so", SPP) | multi (needs NGPU) | scale (needs NGPU)
 set -u
 TAG=$1; shift
 OUT=gpurun_out; mkdir -p $OUT
@@ -32,6 +32,11 @@ for stage in "$@"; do
                      $PY bench.py --workload soup_10m --steps 1 --warmup 3 --spp 4 --no-cpu-baseline --no-e2e > $OUT/${TAG}_ncu_soup10m.log 2>&1; ls -la $OUT/${TAG}_soup10m_k_wf_trace.ncu-rep ;;
     ncu_s7_4)     timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_wf_trace -s 200 -c 1 -o $OUT/${TAG}_s7_4_k_wf_trace -f \
                      $PY bench.py --workload s7_4 --steps 1 --warmup 3 --spp 32 --no-cpu-baseline --no-e2e > $OUT/${TAG}_ncu_s7_4.log 2>&1; ls -la $OUT/${TAG}_s7_4_k_wf_trace.ncu-rep ;;
+    ncu_frame)    # steady-state launch of the roofline leg's shape (one slot group): WORKLOAD, NCU_SPP, NCU_SKIP, KERNEL
+                  W=${WORKLOAD:-sponza}; K=${KERNEL:-k_wf_trace}
+                  timeout 900 $PY tools/ncu_frame.py --workload $W --spp ${NCU_SPP:-8} > $OUT/${TAG}_frame_${W}.json 2>/dev/null; cat $OUT/${TAG}_frame_${W}.json
+                  timeout 900 ncu --set full --clock-control none --import-source on -k regex:$K -s ${NCU_SKIP:-20} -c 1 -o $OUT/${TAG}_${W}_$K -f \
+                     $PY tools/ncu_frame.py --workload $W --spp ${NCU_SPP:-8} > $OUT/${TAG}_ncu_frame_${W}_$K.log 2>&1; ls -la $OUT/${TAG}_${W}_$K.ncu-rep ;;
     variants)     # A/B of library variants built with `make OBJ=.. LIB=..`: RTB_LIB=<file> selects the library the binding loads
                   for v in $VARIANTS; do
                     echo "--- $v"
