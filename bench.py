@@ -329,9 +329,10 @@ def roofline(r):
     achieved = bytes_all / (kernel_ms * 1e-3) * 1e-9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tpath):
+    if os.path.exists(tpath):   # one ncu capture per scene, of a whole-canvas launch: only quoted for a rank that renders that canvas
         t = json.load(open(tpath)).get(r["scene"])
-        traffic = t.get("dram_bytes_per_launch") if t else None
+        if t and list(t.get("canvas", [])) == [r["W"], r["H"]] and rows == r["H"]:
+            traffic = t.get("dram_bytes_per_launch")
     n_samples = rows * r["W"] * s_local
     rays = max(1.0, st["closest_hit_rays"] * scale)
     l2_bytes = torch.cuda.get_device_properties(sc.device).L2_cache_size
