@@ -21,7 +21,8 @@ for stage in "$@"; do
     bench_short)  timeout 600 $PY bench.py --steps 3 --warmup 3 --spp $SPP --no-cpu-baseline --no-e2e > $OUT/${TAG}_bench_spp$SPP.json 2> $OUT/${TAG}_bench_spp$SPP.err; cut -c1-300 $OUT/${TAG}_bench_spp$SPP.json ;;
     bench_s7_4)   timeout 600 $PY bench.py --workload s7_4 --steps 3 --warmup 3 --no-cpu-baseline > $OUT/${TAG}_bench_s7_4.json 2> $OUT/${TAG}_bench_s7_4.err; cut -c1-300 $OUT/${TAG}_bench_s7_4.json ;;
     bench_soup10m) timeout 900 $PY bench.py --workload soup_10m --steps 3 --warmup 3 --cpu-sample 480x270x1 > $OUT/${TAG}_bench_soup10m.json 2> $OUT/${TAG}_bench_soup10m.err; cut -c1-400 $OUT/${TAG}_bench_soup10m.json ;;
-    closest_hit)  timeout 600 $PY tools/bench_closest_hit.py --rays 64000000 > $OUT/${TAG}_closest_hit.jsonl 2> $OUT/${TAG}_closest_hit.err; cat $OUT/${TAG}_closest_hit.jsonl ;;
+    closest_hit)  if [ "$NGPU" -gt 1 ]; then trun $NGPU tools/bench_closest_hit.py --rays 64000000 > $OUT/${TAG}_closest_hit_n$NGPU.jsonl 2> $OUT/${TAG}_closest_hit_n$NGPU.err; cat $OUT/${TAG}_closest_hit_n$NGPU.jsonl
+                  else timeout 600 $PY tools/bench_closest_hit.py --rays 64000000 > $OUT/${TAG}_closest_hit.jsonl 2> $OUT/${TAG}_closest_hit.err; cat $OUT/${TAG}_closest_hit.jsonl; fi ;;
     launches)     timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/${TAG}_launches_bench.csv \
                      $PY bench.py --steps 1 --warmup 3 --spp 16 --no-cpu-baseline --no-e2e > $OUT/${TAG}_launches.log 2>&1; $PY tools/launch_share.py $OUT/${TAG}_launches_bench.csv > $OUT/${TAG}_launch_share.txt; cat $OUT/${TAG}_launch_share.txt ;;
     ncu_trace)    timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_wf_trace -s 200 -c 1 -o $OUT/${TAG}_k_wf_trace -f \
