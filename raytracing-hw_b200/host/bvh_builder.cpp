@@ -18,6 +18,7 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <stdexcept>
@@ -69,7 +70,49 @@ struct KeyIdx {
 struct Scratch {
     std::vector<KeyIdx> keys;
     std::vector<float> left_scan, right_scan;
+    std::vector<Box> boxes;   // wide nodes: the triangles' boxes in sorted order (one random gather instead of three)
 };
+
+
+// ---- std::sort, exactly, on several threads.  libstdc++'s std::sort(first, last, comp) is
+//   __introsort_loop(first, last, 2 * lg(n), comp);  __final_insertion_sort(first, last, comp);      (bits/stl_algo.h)
+// The loop cuts [first, last) at __unguarded_partition_pivot and recurses into the RIGHT part, iterating on the left; the
+// two parts never touch each other again, so they can be replayed as independent tasks -- the sequence of comparisons
+// and moves inside each part is the sequential one.  What the loop leaves behind is a sequence of blocks of <= 16
+// elements (or heap-sorted ranges where the depth limit ran out) with  !(y < x)  for x in an earlier, y in a later block;
+// on that the final insertion sort never moves an element out of its block and is a stable insertion sort of every
+// block, which is what __insertion_sort of the block does on the spot.  Same permutation as std::sort for every input
+// (ties included): tests/test_layout.py builds every scene with the sequential and the task-parallel sort.
+inline auto key_comp() { return __gnu_cxx::__ops::__iter_comp_iter([](const KeyIdx &a, const KeyIdx &b) { return a.key < b.key; }); }
+
+void exact_sort_loop(KeyIdx *first, KeyIdx *last, long depth_limit, size_t task_min) {
+    auto comp = key_comp();
+    while (last - first > 16) {
+        if (depth_limit == 0) {
+            std::__partial_sort(first, last, last, comp);   // heapsort, as __introsort_loop falls back to
+            return;
+        }
+        --depth_limit;
+        KeyIdx *cut = std::__unguarded_partition_pivot(first, last, comp);
+        if ((size_t) (last - cut) >= task_min) {
+#pragma omp task firstprivate(cut, last, depth_limit, task_min)
+            exact_sort_loop(cut, last, depth_limit, task_min);
+        } else {
+            exact_sort_loop(cut, last, depth_limit, task_min);
+        }
+        last = cut;
+    }
+    std::__insertion_sort(first, last, comp);
+}
+// must be called from inside a parallel region (tasks); returns when the range is sorted
+void exact_sort_parallel(KeyIdx *first, KeyIdx *last, size_t task_min) {
+    if (first == last) return;
+#pragma omp taskgroup
+    exact_sort_loop(first, last, (long) std::__lg(last - first) * 2, task_min);
+}
+
+// i-th of `parts` equal chunks of [0, n)
+inline size_t chunk_at(size_t n, size_t parts, size_t i) { return n / parts * i + std::min(i, n % parts); }
 
 struct Builder {
     size_t n = 0;
@@ -82,8 +125,35 @@ struct Builder {
 
     uint32_t alloc_pair() { return pool_next.fetch_add(2); }
 
+    size_t wide_cutoff = (size_t) 1 << 17;   // nodes at least this large are worked on by all threads (taskloops)
+    size_t sort_task_min = (size_t) 1 << 15; // a partition's right part of at least this size becomes a task
+    int wide_parts = 64;
+
+    // union of the triangles' boxes in array order (bvh.cpp:130-132); chunked, combined in order: AABB::grow keeps the
+    // EARLIER of two equal bounds (strict compares), so the in-order combination of in-order chunks gives the same bits
+    Box range_box(size_t first, size_t count, bool wide) {
+        Box out;
+        out.reset();
+        if (!wide) {
+            for (size_t i = 0; i < count; ++i) out.grow(tbox[order[first + i]]);
+            return out;
+        }
+        const size_t P = (size_t) wide_parts;
+        std::vector<Box> part(P);
+#pragma omp taskloop default(shared) grainsize(1)
+        for (size_t c = 0; c < P; ++c) {
+            Box b;
+            b.reset();
+            for (size_t i = chunk_at(count, P, c), e = chunk_at(count, P, c + 1); i < e; ++i) b.grow(tbox[order[first + i]]);
+            part[c] = b;
+        }
+        for (size_t c = 0; c < P; ++c)
+            if (chunk_at(count, P, c) < chunk_at(count, P, c + 1)) out.grow(part[c]);
+        return out;
+    }
+
     // buildHelperSAH (bvh.cpp:5-112): returns the partition offset; writes best_dim.
-    size_t split(const Box &node_box, size_t first, size_t count, int32_t &best_dim, Scratch &sc) {
+    size_t split(const Box &node_box, size_t first, size_t count, int32_t &best_dim, Scratch &sc, bool wide) {
         float best_sah = node_box.surface_area() * (float) count;
         // `float best_split = center[2] - 1e-7;` : float minus double literal, rounded back to float (bvh.cpp:20)
         float best_split = (float) ((double) tcenter[(size_t) order[first] * 3 + 2] - 1e-7);
@@ -98,38 +168,106 @@ struct Builder {
         }
 
         sc.keys.resize(count);
-        for (size_t i = 0; i < count; ++i) {
-            const uint32_t t = order[first + i];
-            sc.keys[i] = {tcenter[(size_t) t * 3 + dim], t};
-        }
-        std::sort(sc.keys.begin(), sc.keys.end(), [](const KeyIdx &a, const KeyIdx &b) { return a.key < b.key; });
-        for (size_t i = 0; i < count; ++i) order[first + i] = sc.keys[i].idx;
-
         sc.left_scan.resize(count);
         sc.right_scan.resize(count);
-        Box tmp = tbox[order[first]];
-        sc.left_scan[0] = tmp.surface_area();
-        for (size_t i = 1; i < count; ++i) {
-            tmp.grow(tbox[order[first + i]]);
-            sc.left_scan[i] = tmp.surface_area();
-        }
-        tmp = tbox[order[first + count - 1]];
-        sc.right_scan[count - 1] = tmp.surface_area();
-        for (size_t i = count - 1; i-- > 0;) {
-            tmp.grow(tbox[order[first + i]]);
-            sc.right_scan[i] = tmp.surface_area();
-        }
-        for (size_t i = 0; i + 1 < count; ++i) {
-            const float ls = sc.left_scan[i];
-            const float rs = sc.right_scan[i + 1];
-            const size_t left_count = i + 1;
-            const float metric = ls * (float) left_count + rs * (float) (count - left_count);
-            if (metric < best_sah) {
-                best_sah = metric;
-                result = left_count;
-                best_dim = dim;
-                best_split = (sc.keys[result - 1].key + sc.keys[result].key) * 0.5f;
+        if (!wide) {
+            for (size_t i = 0; i < count; ++i) {
+                const uint32_t t = order[first + i];
+                sc.keys[i] = {tcenter[(size_t) t * 3 + dim], t};
             }
+            std::sort(sc.keys.begin(), sc.keys.end(), [](const KeyIdx &a, const KeyIdx &b) { return a.key < b.key; });
+            for (size_t i = 0; i < count; ++i) order[first + i] = sc.keys[i].idx;
+
+            Box tmp = tbox[order[first]];
+            sc.left_scan[0] = tmp.surface_area();
+            for (size_t i = 1; i < count; ++i) {
+                tmp.grow(tbox[order[first + i]]);
+                sc.left_scan[i] = tmp.surface_area();
+            }
+            tmp = tbox[order[first + count - 1]];
+            sc.right_scan[count - 1] = tmp.surface_area();
+            for (size_t i = count - 1; i-- > 0;) {
+                tmp.grow(tbox[order[first + i]]);
+                sc.right_scan[i] = tmp.surface_area();
+            }
+            for (size_t i = 0; i + 1 < count; ++i) {
+                const float ls = sc.left_scan[i];
+                const float rs = sc.right_scan[i + 1];
+                const size_t left_count = i + 1;
+                const float metric = ls * (float) left_count + rs * (float) (count - left_count);
+                if (metric < best_sah) {
+                    best_sah = metric;
+                    result = left_count;
+                    best_dim = dim;
+                    best_split = (sc.keys[result - 1].key + sc.keys[result].key) * 0.5f;
+                }
+            }
+        } else {
+            // the same, every pass cut into chunks that all threads work on (the sort: exact_sort_parallel)
+            const size_t P = (size_t) wide_parts;
+            KeyIdx *keys = sc.keys.data();
+            uint32_t *ord = order.data() + first;
+            const float *ctr = tcenter.data();
+#pragma omp taskloop default(shared) grainsize(1)
+            for (size_t c = 0; c < P; ++c)
+                for (size_t i = chunk_at(count, P, c), e = chunk_at(count, P, c + 1); i < e; ++i) keys[i] = {ctr[(size_t) ord[i] * 3 + dim], ord[i]};
+            exact_sort_parallel(keys, keys + count, sort_task_min);
+            // prefix / suffix boxes: chunk unions first, then every chunk scans from the union of the chunks before / after it
+            std::vector<Box> pre(P), suf(P);
+            sc.boxes.resize(count);
+            Box *sorted = sc.boxes.data();
+#pragma omp taskloop default(shared) grainsize(1)
+            for (size_t c = 0; c < P; ++c) {
+                const size_t b = chunk_at(count, P, c), e = chunk_at(count, P, c + 1);
+                Box fwd, bwd;
+                fwd.reset();
+                bwd.reset();
+                for (size_t i = b; i < e; ++i) { ord[i] = keys[i].idx; sorted[i] = tbox[keys[i].idx]; fwd.grow(sorted[i]); }
+                for (size_t i = e; i-- > b;) bwd.grow(sorted[i]);
+                pre[c] = fwd;
+                suf[c] = bwd;
+            }
+            std::vector<Box> before(P), after(P);   // union of everything left of chunk c (in order) / right of it (in reverse order)
+            {
+                Box acc;
+                acc.reset();
+                for (size_t c = 0; c < P; ++c) { before[c] = acc; if (chunk_at(count, P, c) < chunk_at(count, P, c + 1)) acc.grow(pre[c]); }
+                acc.reset();
+                for (size_t c = P; c-- > 0;) { after[c] = acc; if (chunk_at(count, P, c) < chunk_at(count, P, c + 1)) acc.grow(suf[c]); }
+            }
+            float *ls = sc.left_scan.data(), *rs = sc.right_scan.data();
+#pragma omp taskloop default(shared) grainsize(1)
+            for (size_t c = 0; c < P; ++c) {
+                const size_t b = chunk_at(count, P, c), e = chunk_at(count, P, c + 1);
+                if (b == e) continue;
+                // (the reference starts its running box AS the first box -- `AABB tmp = sah_bins[0]` -- which equals growing
+                // an empty box by it: every bound of an empty box loses the strict compare)
+                Box tmp = before[c];
+                for (size_t i = b; i < e; ++i) { tmp.grow(sorted[i]); ls[i] = tmp.surface_area(); }
+                tmp = after[c];
+                for (size_t i = e; i-- > b;) { tmp.grow(sorted[i]); rs[i] = tmp.surface_area(); }
+            }
+            // first index whose metric is strictly below everything before it and below the node's own cost
+            struct Best { float v; size_t left; bool any; };
+            std::vector<Best> bests(P);
+            const float start = best_sah;
+#pragma omp taskloop default(shared) grainsize(1)
+            for (size_t c = 0; c < P; ++c) {
+                Best bb{start, 0, false};
+                for (size_t i = chunk_at(count, P, c), e = std::min(chunk_at(count, P, c + 1), count - 1); i < e; ++i) {
+                    const size_t left_count = i + 1;
+                    const float metric = ls[i] * (float) left_count + rs[i + 1] * (float) (count - left_count);
+                    if (metric < bb.v) bb = Best{metric, left_count, true};
+                }
+                bests[c] = bb;
+            }
+            for (size_t c = 0; c < P; ++c)
+                if (bests[c].any && bests[c].v < best_sah) {
+                    best_sah = bests[c].v;
+                    result = bests[c].left;
+                    best_dim = dim;
+                    best_split = (keys[result - 1].key + keys[result].key) * 0.5f;
+                }
         }
         (void) result;
         const int bd = best_dim;
@@ -137,6 +275,12 @@ struct Builder {
         const float *ctr = tcenter.data();
         uint32_t *b = order.data() + first;
         uint32_t *e = b + count;
+        if (wide && bd == dim) {
+            // the range is sorted by the partition key: the predicate is true on a prefix, std::partition's cursors meet
+            // at its end without a swap (bits/stl_algo.h, bidirectional __partition) -- find that end directly
+            const KeyIdx *keys = sc.keys.data();
+            return (size_t) (std::partition_point(keys, keys + count, [bs](const KeyIdx &k) { return k.key < bs; }) - keys);
+        }
         uint32_t *mid = std::partition(b, e, [ctr, bd, bs](uint32_t t) { return ctr[(size_t) t * 3 + bd] < bs; });
         return (size_t) (mid - b);
     }
@@ -146,14 +290,14 @@ struct Builder {
         Scratch local;
         Scratch &sc = sc_in ? *sc_in : local;
         TNode &nd = pool[id];
-        nd.box.reset();
-        for (size_t i = 0; i < count; ++i) nd.box.grow(tbox[order[first + i]]);
+        const bool wide = count >= wide_cutoff && task_cutoff != std::numeric_limits<size_t>::max();
+        nd.box = range_box(first, count, wide);
         if (count <= 4) {
             nd.first = (uint32_t) first;
             nd.count = (uint32_t) count;
             return;
         }
-        const size_t res = split(nd.box, first, count, nd.split_dim, sc);
+        const size_t res = split(nd.box, first, count, nd.split_dim, sc, wide);
         if (res == 0 || res == count) {
             nd.first = (uint32_t) first;
             nd.count = (uint32_t) count;
@@ -231,6 +375,16 @@ void build_bvh(HostTriangles &tris, HostBvh &out, int threads) {
     B.pool_next = 1;   // slot 0 = root; pairs are allocated from 1
 
     if (threads <= 0) threads = omp_get_max_threads();
+    // RTB_BUILD_WIDE=<n>: nodes of >= n triangles take the all-threads path (tests force it onto small scenes)
+    if (const char *e = std::getenv("RTB_BUILD_WIDE")) {
+        const long v = std::atol(e);
+        if (v > 0) {
+            B.wide_cutoff = (size_t) v;
+            B.sort_task_min = std::max<size_t>(17, (size_t) v / 8);
+            B.task_cutoff = std::min(B.task_cutoff, std::max<size_t>(64, (size_t) v / 2));
+            B.wide_parts = 7;
+        }
+    }
     if (threads <= 1 || n < B.task_cutoff) {
         B.task_cutoff = std::numeric_limits<size_t>::max();
         Scratch sc;
@@ -286,8 +440,13 @@ void HostScene::finalize() {
         if (!(m[5] == 0.f && m[6] == 0.f && m[7] == 0.f)) pick.push_back((uint32_t) i);
     }
     if (!pick.empty()) {
-        lights = tris;
-        lights.permute(pick);
+        auto take = [&](const auto &src, auto &dst, size_t stride) {   // lights[i] = tris[pick[i]]
+            if (src.empty()) return;
+            dst.resize(pick.size() * stride);
+            for (size_t i = 0; i < pick.size(); ++i) std::memcpy(&dst[i * stride], &src[(size_t) pick[i] * stride], stride * sizeof(dst[0]));
+        };
+        take(tris.pos, lights.pos, 9); take(tris.nrm, lights.nrm, 9); take(tris.tan, lights.tan, 12); take(tris.uv, lights.uv, 6);
+        take(tris.mesh, lights.mesh, 1); take(tris.source, lights.source, 1);
         build_bvh(lights, light_bvh);
     }
     build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();

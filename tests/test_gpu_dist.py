@@ -91,7 +91,7 @@ def test_render_multi_all_devices(name, W, H, S, host_scene):
     img, st = rtb.render_multi(scenes, rtb.frame_params(W, H, S), rtb.SPLIT_TILE)
     assert np.array_equal(img, one["rgb"]), "tile split over %d devices differs from the one-GPU frame" % NDEV
     assert st["closest_hit_rays"] == one["stats"]["closest_hit_rays"]
-    K = NDEV if S >= NDEV else 2
+    K = NDEV            # rtb_render_dist runs max(substreams, world) streams per pixel; with S < K the surplus streams are empty
     kone = scenes[0].render(W, H, S, substreams=K)
     img2, st2 = rtb.render_multi(scenes, rtb.frame_params(W, H, S, substreams=K), rtb.SPLIT_SAMPLE)
     diff = np.abs(img2.astype(np.int32) - kone["rgb"].astype(np.int32))

@@ -81,6 +81,31 @@ def test_soup_layout_equals_reference(n_tris, half, ref):
 
 
 @pytest.mark.ref
+@pytest.mark.parametrize("wide", ["300", "5000"])
+def test_all_threads_path_of_big_nodes_equals_reference(wide, ref, monkeypatch):
+    """nodes of >= 128 k triangles are split by all threads together: std::sort replayed as tasks (same partitions, per-block
+    insertion sort), chunked box scans, the partition point found by search.  RTB_BUILD_WIDE forces that path onto small
+    nodes: the layout must stay the reference's, ties included (the axis-aligned Sponza stand-in is full of equal centroids)"""
+    monkeypatch.setenv("RTB_BUILD_WIDE", wide)
+    tri = _util.gen_scenes.soup_triangles(100000, seed=1234, half_extent=4.64).reshape(-1, 9)
+    # duplicates on purpose: exact ties inside big nodes
+    tri[5000:9000] = tri[1000:5000]
+    hs = _util.rtb.HostScene.from_triangles(tri, emissive_from=100000 - 3)
+    rs = ref.RefScene.from_triangles(tri, emissive_from=100000 - 3)
+    a, l = hs.nodes()
+    ra, rl = rs.nodes()
+    assert np.array_equal(a, ra) and np.array_equal(l.astype(np.int64), rl)
+    assert np.array_equal(hs.tris()["pos"], rs.tris()["pos"])
+    p = _util.scene_path("sponza_small")
+    hs = _util.rtb.HostScene.load_gltf(p, 64, 48, 4)
+    rs = ref.RefScene.from_gltf(p, 64, 48, 4)
+    a, l = hs.nodes()
+    ra, rl = rs.nodes()
+    assert np.array_equal(a, ra) and np.array_equal(l.astype(np.int64), rl)
+    assert np.array_equal(hs.tris()["pos"], rs.tris()["pos"]) and np.array_equal(hs.tris()["mesh"], rs.tris()["mesh"])
+
+
+@pytest.mark.ref
 def test_gltf_scene_equals_reference_fully(ref):
     """every array of the flat scene, including textures and materials, against the reference's Scene"""
     p = _util.scene_path("sponza_small")

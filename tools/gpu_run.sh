@@ -48,7 +48,7 @@ for stage in "$@"; do
     scale)        for split in sample tile; do
                     trun $NGPU bench.py --gpus $NGPU --steps ${STEPS:-3} --warmup 3 --split $split > $OUT/${TAG}_bench_n${NGPU}_$split.json 2> $OUT/${TAG}_bench_n${NGPU}_$split.err; cut -c1-300 $OUT/${TAG}_bench_n${NGPU}_$split.json
                   done ;;
-    scale_soup10m) trun $NGPU bench.py --gpus $NGPU --workload soup_10m --steps 3 --warmup 3 --split tile > $OUT/${TAG}_bench_soup10m_n${NGPU}_tile.json 2> $OUT/${TAG}_bench_soup10m_n${NGPU}_tile.err; cut -c1-300 $OUT/${TAG}_bench_soup10m_n${NGPU}_tile.json ;;
+    scale_soup10m) SP=${SPLIT:-sample}; trun $NGPU bench.py --gpus $NGPU --workload soup_10m --steps ${STEPS:-3} --warmup 3 --split $SP > $OUT/${TAG}_bench_soup10m_n${NGPU}_$SP.json 2> $OUT/${TAG}_bench_soup10m_n${NGPU}_$SP.err; cut -c1-300 $OUT/${TAG}_bench_soup10m_n${NGPU}_$SP.json ;;
     *) echo "unknown stage $stage" ;;
   esac
 done
