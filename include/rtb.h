@@ -162,6 +162,12 @@ int rtb_host_scene_desc(const rtb_host_scene *hs, rtb_scene_desc *desc);
 /* BVH statistics the reference prints (src/core/scene.cpp:233-246): counts[0..4] = nodes with 0..4 primitives */
 int rtb_host_scene_bvh_stats(const rtb_host_scene *hs, uint64_t *n_nodes, uint64_t counts5[5], uint64_t *max_leaf);
 double rtb_host_scene_build_seconds(const rtb_host_scene *hs);
+/* Where BVH::buildBVH (src/core/bvh.cpp:5-175) ran for the scene's triangles.  out8: {1 if the GPU builder cut the tree's
+ * large nodes (csrc/rtb_build.cu) else 0, levels, partition rounds, heap-sorted ranges, nodes handed back to the host
+ * uncut, GPU seconds incl. copies, kernel seconds, 0}.  The layout is the reference's either way (tests/test_layout.py,
+ * tests/test_gpu_build.py).  RTB_BUILD_GPU=0|1 forces the choice (default: scenes of >= 500 k triangles when a device exists),
+ * RTB_BUILD_GPU_BELOW=<n> (default 5: the whole tree on the GPU) sets the node size below which the host carries on.                              */
+int rtb_host_scene_build_info(const rtb_host_scene *hs, double out8[8]);
 void rtb_host_scene_destroy(rtb_host_scene *hs);
 
 /* ------------------------------------------------------------------------------------------------ device side */

@@ -24,7 +24,7 @@ REQUEST_COUNTERS = 0xFFFFFFFFFFFFFFFF
 ABI_SYMBOLS = [
     "rtb_last_error", "rtb_device_count",
     "rtb_host_scene_load_gltf", "rtb_host_scene_from_triangles", "rtb_host_scene_desc", "rtb_host_scene_bvh_stats",
-    "rtb_host_scene_build_seconds", "rtb_host_scene_destroy",
+    "rtb_host_scene_build_seconds", "rtb_host_scene_build_info", "rtb_host_scene_destroy",
     "rtb_host_scene_raw_geometry", "rtb_scene_create_raw", "rtb_scene_read_buffer",
     "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_device", "rtb_scene_traversal_bytes", "rtb_scene_upload_bytes", "rtb_scene_launches", "rtb_scene_stage_ms",
     "rtb_closest_hit", "rtb_closest_hit_device", "rtb_light_pdf", "rtb_measure_l2",
@@ -113,6 +113,7 @@ def lib():
         L.rtb_last_error.restype = C.c_char_p
         L.rtb_host_scene_build_seconds.restype = C.c_double
         L.rtb_host_scene_build_seconds.argtypes = [C.c_void_p]
+        L.rtb_host_scene_build_info.argtypes = [C.c_void_p, C.POINTER(C.c_double * 8)]
         L.rtb_scene_traversal_bytes.restype = C.c_size_t
         L.rtb_scene_traversal_bytes.argtypes = [C.c_void_p]
         L.rtb_scene_upload_bytes.restype = C.c_size_t
@@ -252,6 +253,13 @@ class HostScene:
     @property
     def build_seconds(self):
         return lib().rtb_host_scene_build_seconds(self.h)
+
+    def build_info(self):
+        """where the BVH was built: dict(on_gpu, levels, rounds, heap_ranges, host_fallback_nodes, gpu_seconds, kernel_seconds)"""
+        o = (C.c_double * 8)()
+        _check(lib().rtb_host_scene_build_info(self.h, C.byref(o)))
+        return dict(on_gpu=bool(o[0]), levels=int(o[1]), rounds=int(o[2]), heap_ranges=int(o[3]), host_fallback_nodes=int(o[4]),
+                    gpu_seconds=o[5], kernel_seconds=o[6])
 
     def bvh_stats(self):
         n, c, m = C.c_uint64(), (C.c_uint64 * 5)(), C.c_uint64()

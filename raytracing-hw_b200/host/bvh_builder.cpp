@@ -14,18 +14,37 @@
 // surface_area = 2*((xy + xz) + yz) (primitive.h:48-51).  This TU must be compiled WITHOUT -ffast-math and
 // without FMA contraction (-ffp-contract=off), like the reference's x86-64 baseline build.
 #include "host_scene.h"
+#include "../csrc/rtb_build.h"
 
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <cstdio>
 #include <cstdlib>
+#include <new>
 #include <cstring>
 #include <limits>
 #include <stdexcept>
 #include <omp.h>
+#include <sys/mman.h>
 
 namespace rtb {
 namespace {
+
+// Large work arrays are first touched right after they are allocated; with 4 KB pages that is ~100 k page faults per array
+// at 10 M triangles (0.1 - 0.5 s each, and they serialise across threads).  Ask for transparent huge pages on the part of
+// the block that is 2 MB aligned (a no-op where the kernel does not offer them).
+inline void advise_huge(void *p, size_t bytes) {
+    const uintptr_t a = ((uintptr_t) p + ((uintptr_t) 2 << 20) - 1) & ~(((uintptr_t) 2 << 20) - 1);
+    const uintptr_t e = ((uintptr_t) p + bytes) & ~(((uintptr_t) 2 << 20) - 1);
+    if (e > a) madvise((void *) a, (size_t) (e - a), MADV_HUGEPAGE);
+}
+template <class V>
+void resize_huge(V &v, size_t count) {
+    v.reserve(count);
+    if (count * sizeof(v[0]) >= ((size_t) 8 << 20)) advise_huge(v.data(), count * sizeof(v[0]));
+    v.resize(count);
+}
 
 struct Box {
     float mn[3], mx[3];
@@ -83,6 +102,11 @@ struct Scratch {
 // on that the final insertion sort never moves an element out of its block and is a stable insertion sort of every
 // block, which is what __insertion_sort of the block does on the spot.  Same permutation as std::sort for every input
 // (ties included): tests/test_layout.py builds every scene with the sequential and the task-parallel sort.
+// RTB_BUILD_SORT_DEPTH=<d>: introsort's depth limit (2 * lg(n)) replaced by d in every sort of the build, host and GPU
+// alike -- lets the tests reach the heap-sorted ranges that real inputs almost never produce
+// (read once per build_bvh call)
+int g_sort_depth = -1;
+int sort_depth_override() { return g_sort_depth; }
 inline auto key_comp() { return __gnu_cxx::__ops::__iter_comp_iter([](const KeyIdx &a, const KeyIdx &b) { return a.key < b.key; }); }
 
 void exact_sort_loop(KeyIdx *first, KeyIdx *last, long depth_limit, size_t task_min) {
@@ -107,8 +131,20 @@ void exact_sort_loop(KeyIdx *first, KeyIdx *last, long depth_limit, size_t task_
 // must be called from inside a parallel region (tasks); returns when the range is sorted
 void exact_sort_parallel(KeyIdx *first, KeyIdx *last, size_t task_min) {
     if (first == last) return;
+    const int ov = sort_depth_override();
 #pragma omp taskgroup
-    exact_sort_loop(first, last, (long) std::__lg(last - first) * 2, task_min);
+    exact_sort_loop(first, last, ov >= 0 ? (long) ov : (long) std::__lg(last - first) * 2, task_min);
+}
+// std::sort, or the same loops with the depth limit of sort_depth_override()
+void exact_sort_serial(KeyIdx *first, KeyIdx *last) {
+    const int ov = sort_depth_override();
+    if (ov < 0) {
+        std::sort(first, last, [](const KeyIdx &a, const KeyIdx &b) { return a.key < b.key; });
+    } else if (first != last) {
+        auto comp = key_comp();
+        std::__introsort_loop(first, last, (long) ov, comp);
+        std::__final_insertion_sort(first, last, comp);
+    }
 }
 
 // i-th of `parts` equal chunks of [0, n)
@@ -119,11 +155,19 @@ struct Builder {
     std::vector<Box> tbox;           // Primitive::aabb() cache (primitive.cpp:63-75)
     std::vector<float> tcenter;      // n x 3
     std::vector<uint32_t> order;
-    std::vector<TNode> pool;
+    // node pool: 2 n + 1 slots of address space, touched only where nodes are made (value-initialising 2 n + 1 records up
+    // front cost 0.5 s of page faults at 10 M triangles)
+    TNode *pool = nullptr;
     std::atomic<uint32_t> pool_next{0};
+    ~Builder() { std::free(pool); }
     size_t task_cutoff = 1 << 14;
 
-    uint32_t alloc_pair() { return pool_next.fetch_add(2); }
+    uint32_t alloc_pair() {
+        const uint32_t p = pool_next.fetch_add(2);
+        new (&pool[p]) TNode();
+        new (&pool[p + 1]) TNode();
+        return p;
+    }
 
     size_t wide_cutoff = (size_t) 1 << 17;   // nodes at least this large are worked on by all threads (taskloops)
     size_t sort_task_min = (size_t) 1 << 15; // a partition's right part of at least this size becomes a task
@@ -175,7 +219,7 @@ struct Builder {
                 const uint32_t t = order[first + i];
                 sc.keys[i] = {tcenter[(size_t) t * 3 + dim], t};
             }
-            std::sort(sc.keys.begin(), sc.keys.end(), [](const KeyIdx &a, const KeyIdx &b) { return a.key < b.key; });
+            exact_sort_serial(sc.keys.data(), sc.keys.data() + count);
             for (size_t i = 0; i < count; ++i) order[first + i] = sc.keys[i].idx;
 
             Box tmp = tbox[order[first]];
@@ -320,17 +364,64 @@ struct Builder {
         TNode &me = pool[id];
         me.desc = 2 + pool[pair].desc + pool[pair + 1].desc;
     }
+
+    // The part of the tree the GPU built (csrc/rtb_build.cu) becomes pool nodes -- with the SAME indices (the root is 0 and
+    // the children of a node are a pair in both) -- in one linear pass; the ranges it handed back are built here, in
+    // parallel; the subtree sizes then follow from one backward sweep (children have larger indices than their parents).
+    void adopt_all(const std::vector<GpuTopNode> &top) {
+        const size_t nt = top.size();
+        pool_next = (uint32_t) nt;
+        std::vector<uint32_t> todo;
+#pragma omp parallel
+        {
+            std::vector<uint32_t> mine;
+#pragma omp for schedule(static) nowait
+            for (size_t t = 0; t < nt; ++t) {
+                const GpuTopNode &g = top[t];
+                TNode *nd = new (&pool[t]) TNode();
+                if (g.kind == kTopHost) { mine.push_back((uint32_t) t); continue; }
+                for (int k = 0; k < 3; ++k) { nd->box.mn[k] = g.box[k]; nd->box.mx[k] = g.box[3 + k]; }
+                nd->split_dim = g.split_dim;
+                if (g.kind == kTopLeaf) {
+                    nd->first = g.first;
+                    nd->count = g.count;
+                } else {
+                    nd->left = g.left;
+                    nd->right = g.right;
+                }
+            }
+#pragma omp critical
+            todo.insert(todo.end(), mine.begin(), mine.end());
+        }
+        // large ranges first (they spawn tasks of their own), the many small ones dealt out dynamically
+        std::sort(todo.begin(), todo.end(), [&](uint32_t x, uint32_t y) { return top[x].count != top[y].count ? top[x].count > top[y].count : x < y; });
+#pragma omp parallel
+#pragma omp single
+        {
+#pragma omp taskloop default(shared) grainsize(16)
+            for (size_t i = 0; i < todo.size(); ++i) {
+                const GpuTopNode &g = top[todo[i]];
+                build(todo[i], g.first, g.count, nullptr);
+            }
+        }
+        for (size_t t = nt; t-- > 0;) {
+            TNode &nd = pool[t];
+            if (top[t].kind == kTopInternal) nd.desc = 2 + pool[nd.left].desc + pool[nd.right].desc;
+        }
+    }
 };
 
 }  // namespace
 
+// (called from inside a parallel region: the loops are taskloops)
 void HostTriangles::permute(const std::vector<uint32_t> &order) {
     const size_t n = order.size();
     auto apply = [&](auto &vec, size_t stride) {
         using T = typename std::remove_reference<decltype(vec)>::type;
         if (vec.empty()) return;   // (an attribute array that has not been assembled)
-        T out(n * stride);
-#pragma omp parallel for schedule(static)
+        T out;
+        resize_huge(out, n * stride);
+#pragma omp taskloop default(shared) grainsize(65536)
         for (size_t i = 0; i < n; ++i)
             std::memcpy(&out[i * stride], &vec[(size_t) order[i] * stride], stride * sizeof(out[0]));
         vec.swap(out);
@@ -350,11 +441,23 @@ void build_bvh(HostTriangles &tris, HostBvh &out, int threads) {
     if (n == 0) throw std::runtime_error("No primitives for node 0");   // bvh.cpp:122-123
     if (n >= (size_t) 1 << 30) throw std::runtime_error("too many triangles");
 
+    {
+        const char *e = std::getenv("RTB_BUILD_SORT_DEPTH");
+        g_sort_depth = e && *e ? std::max(0, std::atoi(e)) : -1;
+    }
+    const bool verbose = std::getenv("RTB_BUILD_VERBOSE") != nullptr;
+    auto t_mark = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        if (!verbose) return;
+        const auto now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[build_bvh] %-28s %.3f s\n", what, std::chrono::duration<double>(now - t_mark).count());
+        t_mark = now;
+    };
     Builder B;
     B.n = n;
-    B.tbox.resize(n);
-    B.tcenter.resize(n * 3);
-    B.order.resize(n);
+    resize_huge(B.tbox, n);
+    resize_huge(B.tcenter, n * 3);
+    resize_huge(B.order, n);
 #pragma omp parallel for schedule(static)
     for (size_t i = 0; i < n; ++i) {
         const float *p = &tris.pos[i * 9];
@@ -371,9 +474,13 @@ void build_bvh(HostTriangles &tris, HostBvh &out, int threads) {
         for (int k = 0; k < 3; ++k) B.tcenter[i * 3 + k] = b.center(k);
         B.order[i] = (uint32_t) i;
     }
-    B.pool.resize(2 * n + 1);
+    B.pool = static_cast<TNode *>(std::malloc((2 * n + 1) * sizeof(TNode)));
+    if (!B.pool) throw std::runtime_error("out of memory for the BVH node pool");
+    if (n >= ((size_t) 1 << 18)) advise_huge(B.pool, (2 * n + 1) * sizeof(TNode));
+    new (&B.pool[0]) TNode();
     B.pool_next = 1;   // slot 0 = root; pairs are allocated from 1
 
+    lap("triangle boxes / centres");
     if (threads <= 0) threads = omp_get_max_threads();
     // RTB_BUILD_WIDE=<n>: nodes of >= n triangles take the all-threads path (tests force it onto small scenes)
     if (const char *e = std::getenv("RTB_BUILD_WIDE")) {
@@ -385,7 +492,33 @@ void build_bvh(HostTriangles &tris, HostBvh &out, int threads) {
             B.wide_parts = 7;
         }
     }
-    if (threads <= 1 || n < B.task_cutoff) {
+    // RTB_BUILD_GPU: 0 never, 1 whenever a device is there, unset: scenes of >= 500 k triangles.  RTB_BUILD_GPU_BELOW: nodes with
+    // fewer triangles than this are built on the host (>= 5; 5, the default = the whole tree on the GPU).
+    bool on_gpu = false;
+    {
+        const char *e = std::getenv("RTB_BUILD_GPU");
+        const int mode = e && *e ? std::atoi(e) : -1;
+        size_t below = 5;   // the whole tree: measured fastest (profiles/r02g_build_time.jsonl)
+        if (const char *b = std::getenv("RTB_BUILD_GPU_BELOW")) below = (size_t) std::max(5L, std::atol(b));
+        if (mode != 0 && (mode > 0 || n >= (size_t) 500000) && n >= below && threads != 1) {
+            std::vector<GpuTopNode> top;
+            std::vector<uint32_t> ord;
+            GpuBuildStats gs;
+            std::string err;
+            if (gpu_build_top(reinterpret_cast<const float *>(B.tbox.data()), B.tcenter.data(), n, below, -1, sort_depth_override(), top, ord, gs, err)) {
+                B.order.swap(ord);
+                out.gpu = gs;
+                out.built_on_gpu = true;
+                lap("GPU levels (incl. copies)");
+                B.adopt_all(top);
+                on_gpu = true;
+            } else if (mode > 0 && std::getenv("RTB_BUILD_GPU_STRICT")) {
+                throw std::runtime_error("GPU BVH build failed: " + err);
+            }
+        }
+    }
+    if (on_gpu) {
+    } else if (threads <= 1 || n < B.task_cutoff) {
         B.task_cutoff = std::numeric_limits<size_t>::max();
         Scratch sc;
         B.build(0, 0, n, &sc);
@@ -395,36 +528,60 @@ void build_bvh(HostTriangles &tris, HostBvh &out, int threads) {
         B.build(0, 0, n, nullptr);
     }
 
+    lap("host nodes");
     // Reference numbering: nodes = [root] + desc(root); desc(X) = [L, R] + desc(R) + desc(L).
     const size_t total = 1 + (size_t) B.pool[0].desc;
-    out.aabb.resize(total * 6);
-    out.links.resize(total * 5);
-    struct Item { uint32_t pool_id; uint32_t ref_id; uint32_t desc_base; };
-    std::vector<Item> stack;
-    stack.push_back({0, 0, 1});
-    while (!stack.empty()) {
-        const Item it = stack.back();
-        stack.pop_back();
-        const TNode &t = B.pool[it.pool_id];
-        float *a = &out.aabb[(size_t) it.ref_id * 6];
-        for (int k = 0; k < 3; ++k) { a[k] = t.box.mn[k]; a[3 + k] = t.box.mx[k]; }
-        int32_t *l = &out.links[(size_t) it.ref_id * 5];
-        l[2] = t.split_dim;
-        if (t.left < 0) {
-            l[0] = -1; l[1] = -1;
-            l[3] = (int32_t) t.first;
-            l[4] = (int32_t) t.count;
-        } else {
-            const uint32_t L = it.desc_base, R = it.desc_base + 1;
-            l[0] = (int32_t) L; l[1] = (int32_t) R;
-            l[3] = -1; l[4] = 0;
-            const uint32_t r_base = it.desc_base + 2;
-            const uint32_t l_base = r_base + B.pool[t.right].desc;
-            stack.push_back({(uint32_t) t.left, L, l_base});
-            stack.push_back({(uint32_t) t.right, R, r_base});
+    resize_huge(out.aabb, total * 6);
+    resize_huge(out.links, total * 5);
+    // (the number of every node follows from the sizes of the subtrees alone, so the subtrees are numbered in parallel)
+    struct Numberer {
+        const Builder &B;
+        HostBvh &out;
+        void run(uint32_t pool_id, uint32_t ref_id, uint32_t desc_base) const {
+            while (true) {
+                const TNode &t = B.pool[pool_id];
+                float *a = &out.aabb[(size_t) ref_id * 6];
+                for (int k = 0; k < 3; ++k) { a[k] = t.box.mn[k]; a[3 + k] = t.box.mx[k]; }
+                int32_t *l = &out.links[(size_t) ref_id * 5];
+                l[2] = t.split_dim;
+                if (t.left < 0) {
+                    l[0] = -1; l[1] = -1;
+                    l[3] = (int32_t) t.first;
+                    l[4] = (int32_t) t.count;
+                    return;
+                }
+                const uint32_t L = desc_base, R = desc_base + 1;
+                l[0] = (int32_t) L; l[1] = (int32_t) R;
+                l[3] = -1; l[4] = 0;
+                const uint32_t r_base = desc_base + 2;
+                const uint32_t l_base = r_base + B.pool[t.right].desc;
+                const uint32_t right = (uint32_t) t.right, left = (uint32_t) t.left;
+                if (t.desc >= 8192) {
+#pragma omp task firstprivate(right, R, r_base)
+                    run(right, R, r_base);
+                } else {
+                    run(right, R, r_base);
+                }
+                pool_id = left;
+                ref_id = L;
+                desc_base = l_base;
+            }
+        }
+    };
+    {
+        const Numberer nb{B, out};
+#pragma omp parallel num_threads(threads)
+#pragma omp single
+        {
+#pragma omp taskgroup
+            {
+#pragma omp task default(shared)
+                nb.run(0, 0, 1);
+                tris.permute(B.order);   // independent of the numbering: both run on the same team
+            }
         }
     }
-    tris.permute(B.order);
+    lap("numbering + triangle permutation");
 }
 
 void HostScene::finalize() {

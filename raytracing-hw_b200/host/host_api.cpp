@@ -209,6 +209,20 @@ int rtb_host_scene_bvh_stats(const rtb_host_scene *hs, uint64_t *n_nodes, uint64
 
 double rtb_host_scene_build_seconds(const rtb_host_scene *hs) { return hs ? hs->s.build_seconds : 0.0; }
 
+int rtb_host_scene_build_info(const rtb_host_scene *hs, double out8[8]) {
+    if (!hs || !out8) return RTB_ERR_INVALID;
+    const rtb::HostBvh &b = hs->s.bvh;
+    out8[0] = b.built_on_gpu ? 1.0 : 0.0;
+    out8[1] = b.gpu.levels;
+    out8[2] = (double) b.gpu.rounds;
+    out8[3] = (double) b.gpu.heap_ranges;
+    out8[4] = (double) b.gpu.host_fallback_nodes;
+    out8[5] = b.gpu.seconds;
+    out8[6] = b.gpu.kernel_seconds;
+    out8[7] = 0.0;
+    return RTB_OK;
+}
+
 void rtb_host_scene_destroy(rtb_host_scene *hs) { delete hs; }
 
 int rtb_write_ppm(const char *path, int width, int height, const uint8_t *rgb8) {

@@ -5,6 +5,8 @@
 #include <string>
 #include <vector>
 
+#include "../csrc/rtb_build.h"
+
 namespace rtb {
 
 struct HostTexture {
@@ -16,6 +18,8 @@ struct HostTexture {
 struct HostBvh {
     std::vector<float> aabb;      // n x 6
     std::vector<int32_t> links;   // n x 5
+    bool built_on_gpu = false;    // the large nodes were cut by csrc/rtb_build.cu (same layout)
+    GpuBuildStats gpu;
     size_t size() const { return links.size() / 5; }
 };
 

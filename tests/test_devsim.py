@@ -213,6 +213,18 @@ def test_libm_known_answers():
     assert r.returncode == 0, r.stdout
 
 
+def test_gpu_builder_sort_replay_equals_std_sort():
+    """the GPU builder's sort (csrc/rtb_build_steps.cuh: introsort replayed breadth first, one partition step of every live
+    range per round; heap-sorted ranges with libstdc++'s own moves) driven by plain loops and compared with std::sort /
+    std::__partial_sort themselves on distinct, tied, sorted, reversed, all-equal and organ-pipe keys, one and many segments"""
+    import os
+    import subprocess
+    exe = os.path.join(_util.ROOT, "tests", "devsim", "build_check")
+    subprocess.run(["make", "-C", os.path.dirname(exe), "build_check"], check=True, stdout=subprocess.DEVNULL)
+    r = subprocess.run([exe, "4"], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.startswith("ok"), r.stdout
+
+
 def _big_leaf_scene():
     """40 + 9 coincident triangles (their centroids cannot be split: leaves of 40 and 9 triangles, and every ray that hits
     them produces exact ties, which the first triangle in the reference's order must win) among 300 random ones"""
