@@ -346,7 +346,7 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
     int rc;
     fill_lut(L.lut);
     std::vector<DTexture> tex(desc->n_textures);
-    std::vector<const void *> tex_ptr(desc->n_textures, nullptr);
+    std::vector<const void *> tex_ptr(desc->n_textures, nullptr), quad_ptr(desc->n_textures, nullptr);
     Uploader up;
     auto add = [&up](const auto &v, auto **dst) { up.add(v.data(), v.size() * sizeof(v[0]), (const void **) dst); };
     add(L.bvh.nodes, &sc->d.bvh.nodes);
@@ -367,9 +367,10 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
     for (uint32_t i = 0; i < desc->n_textures; ++i) {
         const rtb_texture_desc &t = desc->textures[i];
         up.add(t.rgba, (size_t) t.width * t.height * 4, &tex_ptr[i]);
+        up.add(nullptr, (size_t) t.width * t.height * 16, &quad_ptr[i]);   // DTexture::quads, written on the device
     }
     if ((rc = up.alloc(sc)) != RTB_OK) return fail(rc);
-    for (uint32_t i = 0; i < desc->n_textures; ++i) tex[i] = {(const uchar4 *) tex_ptr[i], desc->textures[i].width, desc->textures[i].height};
+    for (uint32_t i = 0; i < desc->n_textures; ++i) tex[i] = {(const uchar4 *) tex_ptr[i], (const uint4 *) quad_ptr[i], desc->textures[i].width, desc->textures[i].height};
     if ((rc = up.run(sc)) != RTB_OK) return fail(rc);
     fill_bvh_scalars(L.bvh, sc->d.bvh, desc->n_tris);
     if (desc->n_lights > 0) fill_bvh_scalars(L.light_bvh, sc->d.light_bvh, desc->n_lights);
@@ -380,6 +381,12 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
 
     // (failures from here on still go through fail(): the scene and its device arena are released)
     if ((rc = finish_scene(sc, "rtb_scene_create")) != RTB_OK) return fail(rc);
+    for (const DTexture &t : tex) launch_texture_quads(t, sc->streams[0]);
+    {
+        cudaError_t ce = cudaStreamSynchronize(sc->streams[0]);
+        if (ce == cudaSuccess) ce = cudaGetLastError();
+        if (ce != cudaSuccess) { rtb::set_error(std::string("rtb_scene_create: ") + cudaGetErrorString(ce)); return fail(RTB_ERR_CUDA); }
+    }
     *out = sc;
     return RTB_OK;
 }
@@ -455,7 +462,7 @@ int rtb_scene_create_raw(const rtb_scene_desc *desc, const rtb_raw_geometry *raw
     int rc;
     fill_lut(L.lut);
     std::vector<DTexture> tex(desc->n_textures);
-    std::vector<const void *> tex_ptr(desc->n_textures, nullptr);
+    std::vector<const void *> tex_ptr(desc->n_textures, nullptr), quad_ptr(desc->n_textures, nullptr);
     auto add = [&up](const auto &v, auto **dst) { up.add(v.data(), v.size() * sizeof(v[0]), (const void **) dst); };
     const size_t nt = desc->n_tris;
     up.add(nullptr, (size_t) n_internal * sizeof(DNode), (const void **) &sc->d.bvh.nodes);
@@ -476,9 +483,10 @@ int rtb_scene_create_raw(const rtb_scene_desc *desc, const rtb_raw_geometry *raw
     for (uint32_t i = 0; i < desc->n_textures; ++i) {
         const rtb_texture_desc &t = desc->textures[i];
         up.add(t.rgba, (size_t) t.width * t.height * 4, &tex_ptr[i]);
+        up.add(nullptr, (size_t) t.width * t.height * 16, &quad_ptr[i]);   // DTexture::quads, written on the device
     }
     if ((rc = up.alloc(sc)) != RTB_OK) return fail(rc);
-    for (uint32_t i = 0; i < desc->n_textures; ++i) tex[i] = {(const uchar4 *) tex_ptr[i], desc->textures[i].width, desc->textures[i].height};
+    for (uint32_t i = 0; i < desc->n_textures; ++i) tex[i] = {(const uchar4 *) tex_ptr[i], (const uint4 *) quad_ptr[i], desc->textures[i].width, desc->textures[i].height};
 
     // ---- the temporary block: raw bytes, reference-order nodes, tables, the two node frontiers
     std::vector<DRawMesh> dmesh(raw->n_meshes);
@@ -535,6 +543,7 @@ int rtb_scene_create_raw(const rtb_scene_desc *desc, const rtb_raw_geometry *raw
     cudaError_t ce = cudaMemsetAsync(words, 0, 256, st);
     int levels = 0;
     if (ce == cudaSuccess) {
+        for (const DTexture &t : tex) launch_texture_quads(t, st);
         launch_assemble_triangles(d_mesh, d_first, (int) raw->n_meshes, d_source, desc->n_tris, const_cast<float4 *>(sc->d.bvh.tris),
                                   const_cast<float4 *>(sc->d.tri_shade), const_cast<float4 *>(sc->d.tri_tan), d_error, st);
         const BigLeafIndex big{d_big_node, d_big_slot, (int) leaf.big_node.size()};

@@ -27,6 +27,13 @@ __global__ void __launch_bounds__(256) k_assemble_triangles(const DRawMesh *mesh
     }
 }
 
+// DTexture::quads of one texture: a thread per texel, coalesced 16-byte stores, the four taps gathered from two rows
+__global__ void __launch_bounds__(256) k_texture_quads(const uchar4 *texels, uint4 *quads, int width, int height) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t) width * (size_t) height) return;
+    quads[i] = texture_quad(texels, width, height, (int) (i % (size_t) width), (int) (i / (size_t) width));
+}
+
 __global__ void __launch_bounds__(256) k_convert_level(const NodeItem *in, const unsigned *n_in_ptr, uint32_t n_nodes, uint32_t n_internal, uint32_t n_tris,
                                                        const float *aabb, const int32_t *links, BigLeafIndex big, DNode *nodes, NodeItem *out,
                                                        unsigned *n_out, int *error) {
@@ -51,6 +58,12 @@ __global__ void k_seed_root(NodeItem *items, unsigned *counts, uint32_t n_nodes)
 }
 
 }  // namespace
+
+void launch_texture_quads(const DTexture &t, cudaStream_t st) {
+    const size_t n = (size_t) t.width * (size_t) t.height;
+    if (n == 0 || !t.quads) return;
+    k_texture_quads<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(t.texels, const_cast<uint4 *>(t.quads), t.width, t.height);
+}
 
 void launch_assemble_triangles(const DRawMesh *d_meshes, const uint32_t *d_mesh_first, int n_meshes, const uint32_t *d_tri_source, uint32_t n_tris,
                                float4 *d_tris, float4 *d_shade, float4 *d_tan, int *d_error, cudaStream_t stream) {

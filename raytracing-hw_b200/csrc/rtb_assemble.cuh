@@ -266,6 +266,13 @@ RTB_HD int convert_node(const NodeItem &it, uint32_t n_nodes, uint32_t n_interna
     return err;
 }
 
+// the bilinear footprint that starts at texel (x, y) of a row-major RGBA8 image, wrapped (DTexture::quads)
+RTB_HD uint4 texture_quad(const uchar4 *texels, int width, int height, int x, int y) {
+    const int x1 = x + 1 >= width ? x + 1 - width : x + 1, y1 = y + 1 >= height ? y + 1 - height : y + 1;
+    const uint32_t *w = reinterpret_cast<const uint32_t *>(texels);
+    return make_uint4(w[(size_t) y * width + x], w[(size_t) y1 * width + x], w[(size_t) y * width + x1], w[(size_t) y1 * width + x1]);
+}
+
 inline const char *assemble_error_text(int e) {
     switch (e) {
         case kAsmVertexIndex: return "[gltf check] vertex index out of range";

@@ -64,8 +64,15 @@ constexpr int kMaxStack = 64;
 constexpr int kTriStride = 4;   // float4 per triangle record (the 4th is padding: a 48-byte record already costs two 32-byte sectors)
 constexpr float kFar = 1e9f;   // `intersection.distance = 1e9` (bvh.cpp:181)
 
+// A texture is read through `quads`: for every texel (x, y) the four taps of the bilinear footprint that starts there --
+// {(x, y), (x, y + 1), (x + 1, y), (x + 1, y + 1)}, wrapped (Texture::interpolate_sample, primitive.h:182-215) -- as one
+// 16-byte record, written on the device when the scene is created (rtb_assemble.cuh: texture_quad).  A bilinear fetch is
+// then ONE 128-bit load = one 32-byte sector instead of four 4-byte loads in two rows (2.25 sectors on average); the shade
+// step is bound by random 32-byte DRAM sectors.  4 x the bytes in HBM (1.1 GB for Sponza's 69
+// textures), the same bytes over PCIe.  `texels` stays the row-major RGBA8 image the file delivered.
 struct DTexture {
     const uchar4 *texels;
+    const uint4 *quads;
     int width, height;
 };
 

@@ -257,6 +257,7 @@ RTB_HD int wrap_index(int i, int n) {   // i % n for 0 <= i <= n + 1
     i = i >= n ? i - n : i;
     return i >= n ? i - n : i;
 }
+RTB_HD uchar4 u2c(uint32_t v) { return make_uchar4((unsigned char) (v & 255u), (unsigned char) ((v >> 8) & 255u), (unsigned char) ((v >> 16) & 255u), (unsigned char) (v >> 24)); }
 template <bool SRGB>
 RTB_HD void texture_sample(const DScene &sc, int tex, float px, float py, float out[4]) {
     const DTexture t = sc.textures[tex];
@@ -266,13 +267,15 @@ RTB_HD void texture_sample(const DScene &sc, int tex, float px, float py, float 
     py = py * (float) t.height;
     const int ix = (int) floorf(px), iy = (int) floorf(py);
     const float dx = px - floorf(px), dy = py - floorf(py);
-    // 0 <= ix <= width (px lies in [0,1] after the wrap), so `% width` is at most two conditional subtractions
-    const int x0 = wrap_index(ix, t.width), x1 = wrap_index(ix + 1, t.width);
-    const int y0 = wrap_index(iy, t.height), y1 = wrap_index(iy + 1, t.height);
-    const uchar4 c00 = ldg(&t.texels[(size_t) y0 * t.width + x0]);   // (dx=0, dy=0)
-    const uchar4 c01 = ldg(&t.texels[(size_t) y1 * t.width + x0]);   // (dx=0, dy=1)
-    const uchar4 c10 = ldg(&t.texels[(size_t) y0 * t.width + x1]);   // (dx=1, dy=0)
-    const uchar4 c11 = ldg(&t.texels[(size_t) y1 * t.width + x1]);   // (dx=1, dy=1)
+    // 0 <= ix <= width (px lies in [0,1] after the wrap), so `% width` is at most two conditional subtractions; the taps at
+    // (x0 + 1) % width and (y0 + 1) % height ride in the quad of (x0, y0)
+    const int x0 = wrap_index(ix, t.width);
+    const int y0 = wrap_index(iy, t.height);
+    const uint4 q = ldg(&t.quads[(size_t) y0 * t.width + x0]);
+    const uchar4 c00 = u2c(q.x);   // (dx=0, dy=0)
+    const uchar4 c01 = u2c(q.y);   // (dx=0, dy=1)
+    const uchar4 c10 = u2c(q.z);   // (dx=1, dy=0)
+    const uchar4 c11 = u2c(q.w);   // (dx=1, dy=1)
     const unsigned char b00[4] = {c00.x, c00.y, c00.z, c00.w}, b01[4] = {c01.x, c01.y, c01.z, c01.w};
     const unsigned char b10[4] = {c10.x, c10.y, c10.z, c10.w}, b11[4] = {c11.x, c11.y, c11.z, c11.w};
 #pragma unroll

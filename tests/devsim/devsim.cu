@@ -15,6 +15,7 @@ namespace {
 struct SimScene {
     HostLayout L;
     std::vector<DTexture> tex;
+    std::vector<std::vector<uint4>> quads;
     DScene d;
 };
 
@@ -38,8 +39,14 @@ bool make_scene(const rtb_scene_desc *desc, SimScene &s, std::string &err) {
     s.d.mesh_normal_transform = s.L.normal_transform.data();
     s.d.n_meshes = s.L.n_meshes;
     s.tex.resize(desc->n_textures);
-    for (uint32_t i = 0; i < desc->n_textures; ++i)
-        s.tex[i] = {(const uchar4 *) desc->textures[i].rgba, desc->textures[i].width, desc->textures[i].height};
+    s.quads.resize(desc->n_textures);
+    for (uint32_t i = 0; i < desc->n_textures; ++i) {
+        const int w = desc->textures[i].width, h = desc->textures[i].height;
+        s.quads[i].resize((size_t) w * h);
+        for (int y = 0; y < h; ++y)
+            for (int x = 0; x < w; ++x) s.quads[i][(size_t) y * w + x] = texture_quad((const uchar4 *) desc->textures[i].rgba, w, h, x, y);
+        s.tex[i] = {(const uchar4 *) desc->textures[i].rgba, s.quads[i].data(), w, h};
+    }
     s.d.textures = s.tex.data();
     fill_scalars(desc, s.d);
     fill_lut(s.L.lut);
