@@ -395,6 +395,8 @@ def main():
                     "d2h_bytes_per_step": r["W"] * r["H"] * 3},
             "gpu_launches": int(r["launches"]),
             "roofline": roof,
+            # outside the timed region (render seconds exclude load / BVH / upload, reported separately)
+            "scene_build": dict(seconds=round(r["hs"].build_seconds, 4), triangles=int(r["hs"].desc.n_tris), **r["hs"].build_info()),
         }
         if r["world"] == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(r["path"], args.cpu_sample, rays_per_sample)

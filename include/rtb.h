@@ -234,7 +234,7 @@ size_t rtb_scene_traversal_bytes(const rtb_scene *scene);
 size_t rtb_scene_upload_bytes(const rtb_scene *scene);
 
 /* Device blocks of destroyed scenes (scene arena, path state, staging buffers) are kept for the next scene -- at most
- * 8 blocks / RTB_BLOCK_CACHE_MB megabytes (default 4096; 0 = none) per process -- so that re-creating a scene per frame
+ * 8 blocks / RTB_BLOCK_CACHE_MB megabytes (default 8192; 0 = none) per process -- so that re-creating a scene per frame
  * does not pay cudaMalloc / cudaFree of ~1 GB each time.  This call hands all of them back to the driver.             */
 void rtb_release_cached_memory(void);
 /* kernels launched so far by rtb_render / rtb_render_device calls on this scene */

@@ -32,7 +32,7 @@ constexpr unsigned kQueueHeads = 64;
 // Device blocks of destroyed scenes (scene arena, path state, staging) are kept -- a few, bounded -- and handed to the
 // next scene that asks for a block of about that size.  A frame server that uploads a scene per frame otherwise pays
 // cudaMalloc / cudaFree of ~1 GB per frame: cudaFree alone was seen at 0.2 - 1.1 s (profiles/r01m_e2e_probe.txt).
-// RTB_BLOCK_CACHE_MB: the most the cache keeps (default 4096; 0: every block goes straight back to the driver).
+// RTB_BLOCK_CACHE_MB: the most the cache keeps (default 8192; 0: every block goes straight back to the driver).
 namespace rtb {
 namespace {
 struct BlockCache {
@@ -43,7 +43,7 @@ struct BlockCache {
     size_t limit() {
         static const size_t v = [] {
             const char *e = std::getenv("RTB_BLOCK_CACHE_MB");
-            return (size_t) (e ? std::max(0, std::atoi(e)) : 4096) << 20;
+            return (size_t) (e ? std::max(0, std::atoi(e)) : 8192) << 20;
         }();
         return v;
     }
@@ -346,7 +346,8 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
     int rc;
     fill_lut(L.lut);
     std::vector<DTexture> tex(desc->n_textures);
-    std::vector<const void *> tex_ptr(desc->n_textures, nullptr), quad_ptr(desc->n_textures, nullptr);
+    std::vector<const void *> tex_ptr(desc->n_textures, nullptr), quad_ptr(desc->n_textures, nullptr), fused_ptr(L.fused.size(), nullptr);
+    std::vector<DFused> fused(L.fused.size());
     Uploader up;
     auto add = [&up](const auto &v, auto **dst) { up.add(v.data(), v.size() * sizeof(v[0]), (const void **) dst); };
     add(L.bvh.nodes, &sc->d.bvh.nodes);
@@ -364,13 +365,16 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
     }
     add(L.lut, &sc->d.lut);
     add(tex, &sc->d.textures);   // (filled in once the texels' device addresses are known, before the copy runs)
+    add(fused, &sc->d.fused);
+    for (size_t g = 0; g < L.fused.size(); ++g) up.add(nullptr, (size_t) L.fused[g].width * L.fused[g].height * 64, &fused_ptr[g]);
     for (uint32_t i = 0; i < desc->n_textures; ++i) {
         const rtb_texture_desc &t = desc->textures[i];
         up.add(t.rgba, (size_t) t.width * t.height * 4, &tex_ptr[i]);
-        up.add(nullptr, (size_t) t.width * t.height * 16, &quad_ptr[i]);   // DTexture::quads, written on the device
+        if (L.texture_needs_quads[i]) up.add(nullptr, (size_t) t.width * t.height * 16, &quad_ptr[i]);   // DTexture::quads, written on the device
     }
     if ((rc = up.alloc(sc)) != RTB_OK) return fail(rc);
     for (uint32_t i = 0; i < desc->n_textures; ++i) tex[i] = {(const uchar4 *) tex_ptr[i], (const uint4 *) quad_ptr[i], desc->textures[i].width, desc->textures[i].height};
+    for (size_t g = 0; g < L.fused.size(); ++g) fused[g] = {(const uint4 *) fused_ptr[g], L.fused[g].width, L.fused[g].height};
     if ((rc = up.run(sc)) != RTB_OK) return fail(rc);
     fill_bvh_scalars(L.bvh, sc->d.bvh, desc->n_tris);
     if (desc->n_lights > 0) fill_bvh_scalars(L.light_bvh, sc->d.light_bvh, desc->n_lights);
@@ -382,6 +386,10 @@ int rtb_scene_create(const rtb_scene_desc *desc, int device, rtb_scene **out) {
     // (failures from here on still go through fail(): the scene and its device arena are released)
     if ((rc = finish_scene(sc, "rtb_scene_create")) != RTB_OK) return fail(rc);
     for (const DTexture &t : tex) launch_texture_quads(t, sc->streams[0]);
+    for (size_t g = 0; g < L.fused.size(); ++g) {
+        auto px = [&](int ti) { return ti >= 0 ? tex[(size_t) ti].texels : nullptr; };
+        launch_fuse_textures(fused[g], px(L.fused[g].tex[0]), px(L.fused[g].tex[1]), px(L.fused[g].tex[2]), sc->streams[0]);
+    }
     {
         cudaError_t ce = cudaStreamSynchronize(sc->streams[0]);
         if (ce == cudaSuccess) ce = cudaGetLastError();
@@ -462,7 +470,8 @@ int rtb_scene_create_raw(const rtb_scene_desc *desc, const rtb_raw_geometry *raw
     int rc;
     fill_lut(L.lut);
     std::vector<DTexture> tex(desc->n_textures);
-    std::vector<const void *> tex_ptr(desc->n_textures, nullptr), quad_ptr(desc->n_textures, nullptr);
+    std::vector<const void *> tex_ptr(desc->n_textures, nullptr), quad_ptr(desc->n_textures, nullptr), fused_ptr(L.fused.size(), nullptr);
+    std::vector<DFused> fused(L.fused.size());
     auto add = [&up](const auto &v, auto **dst) { up.add(v.data(), v.size() * sizeof(v[0]), (const void **) dst); };
     const size_t nt = desc->n_tris;
     up.add(nullptr, (size_t) n_internal * sizeof(DNode), (const void **) &sc->d.bvh.nodes);
@@ -480,13 +489,16 @@ int rtb_scene_create_raw(const rtb_scene_desc *desc, const rtb_raw_geometry *raw
     }
     add(L.lut, &sc->d.lut);
     add(tex, &sc->d.textures);
+    add(fused, &sc->d.fused);
+    for (size_t g = 0; g < L.fused.size(); ++g) up.add(nullptr, (size_t) L.fused[g].width * L.fused[g].height * 64, &fused_ptr[g]);
     for (uint32_t i = 0; i < desc->n_textures; ++i) {
         const rtb_texture_desc &t = desc->textures[i];
         up.add(t.rgba, (size_t) t.width * t.height * 4, &tex_ptr[i]);
-        up.add(nullptr, (size_t) t.width * t.height * 16, &quad_ptr[i]);   // DTexture::quads, written on the device
+        if (L.texture_needs_quads[i]) up.add(nullptr, (size_t) t.width * t.height * 16, &quad_ptr[i]);   // DTexture::quads, written on the device
     }
     if ((rc = up.alloc(sc)) != RTB_OK) return fail(rc);
     for (uint32_t i = 0; i < desc->n_textures; ++i) tex[i] = {(const uchar4 *) tex_ptr[i], (const uint4 *) quad_ptr[i], desc->textures[i].width, desc->textures[i].height};
+    for (size_t g = 0; g < L.fused.size(); ++g) fused[g] = {(const uint4 *) fused_ptr[g], L.fused[g].width, L.fused[g].height};
 
     // ---- the temporary block: raw bytes, reference-order nodes, tables, the two node frontiers
     std::vector<DRawMesh> dmesh(raw->n_meshes);
@@ -544,6 +556,10 @@ int rtb_scene_create_raw(const rtb_scene_desc *desc, const rtb_raw_geometry *raw
     int levels = 0;
     if (ce == cudaSuccess) {
         for (const DTexture &t : tex) launch_texture_quads(t, st);
+        for (size_t g = 0; g < L.fused.size(); ++g) {
+            auto px = [&](int ti) { return ti >= 0 ? tex[(size_t) ti].texels : nullptr; };
+            launch_fuse_textures(fused[g], px(L.fused[g].tex[0]), px(L.fused[g].tex[1]), px(L.fused[g].tex[2]), st);
+        }
         launch_assemble_triangles(d_mesh, d_first, (int) raw->n_meshes, d_source, desc->n_tris, const_cast<float4 *>(sc->d.bvh.tris),
                                   const_cast<float4 *>(sc->d.tri_shade), const_cast<float4 *>(sc->d.tri_tan), d_error, st);
         const BigLeafIndex big{d_big_node, d_big_slot, (int) leaf.big_node.size()};

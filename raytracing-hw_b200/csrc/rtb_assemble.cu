@@ -59,6 +59,21 @@ __global__ void k_seed_root(NodeItem *items, unsigned *counts, uint32_t n_nodes)
 
 }  // namespace
 
+// DFused::data of one material group: a thread per texel, 64 bytes stored per thread
+__global__ void __launch_bounds__(256) k_fuse_textures(const uchar4 *base, const uchar4 *mr, const uchar4 *nrm, uint4 *out, int width, int height) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t) width * (size_t) height) return;
+    uint4 r[4];
+    fused_texel(base, mr, nrm, width, height, (int) (i % (size_t) width), (int) (i / (size_t) width), r);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) out[i * 4 + k] = r[k];
+}
+void launch_fuse_textures(const DFused &f, const uchar4 *base, const uchar4 *mr, const uchar4 *nrm, cudaStream_t st) {
+    const size_t n = (size_t) f.width * (size_t) f.height;
+    if (n == 0 || !f.data) return;
+    k_fuse_textures<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(base, mr, nrm, const_cast<uint4 *>(f.data), f.width, f.height);
+}
+
 void launch_texture_quads(const DTexture &t, cudaStream_t st) {
     const size_t n = (size_t) t.width * (size_t) t.height;
     if (n == 0 || !t.quads) return;

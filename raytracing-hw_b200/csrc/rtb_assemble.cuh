@@ -273,6 +273,15 @@ RTB_HD uint4 texture_quad(const uchar4 *texels, int width, int height, int x, in
     return make_uint4(w[(size_t) y * width + x], w[(size_t) y1 * width + x], w[(size_t) y * width + x1], w[(size_t) y1 * width + x1]);
 }
 
+// texel (x, y) of a fused record (DFused): the quads of the three textures (null: the material has none there)
+RTB_HD void fused_texel(const uchar4 *base, const uchar4 *mr, const uchar4 *nrm, int width, int height, int x, int y, uint4 out[4]) {
+    const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+    out[kFusedBase] = base ? texture_quad(base, width, height, x, y) : zero;
+    out[kFusedMR] = mr ? texture_quad(mr, width, height, x, y) : zero;
+    out[kFusedNormal] = nrm ? texture_quad(nrm, width, height, x, y) : zero;
+    out[3] = zero;
+}
+
 inline const char *assemble_error_text(int e) {
     switch (e) {
         case kAsmVertexIndex: return "[gltf check] vertex index out of range";

@@ -72,9 +72,19 @@ constexpr float kFar = 1e9f;   // `intersection.distance = 1e9` (bvh.cpp:181)
 // textures), the same bytes over PCIe.  `texels` stays the row-major RGBA8 image the file delivered.
 struct DTexture {
     const uchar4 *texels;
-    const uint4 *quads;
+    const uint4 *quads;      // null when every use of the texture goes through a DFused record
     int width, height;
 };
+// The textures of ONE material that share a size -- base colour, metallic-roughness, normal map: all three are sampled at
+// the same texture coordinate of every shaded hit (primitive.cpp:86-140) -- interleaved per texel: 64 bytes =
+// {quad of the base colour, quad of metallic-roughness, quad of the normal map, unused}, so that the three bilinear
+// fetches of a hit touch ONE 64-byte line (one DRAM burst) instead of three random ones.  Written on the device at scene
+// creation (rtb_assemble.cu: k_fuse_textures).  16 x the RGBA8 bytes in HBM (1.7 GB for Sponza's 25 materials at 1024^2).
+struct DFused {
+    const uint4 *data;       // 4 x uint4 per texel: slot 0 base colour, 1 metallic-roughness, 2 normal map
+    int width, height;
+};
+constexpr int kFusedBase = 0, kFusedMR = 1, kFusedNormal = 2;
 
 struct DBvh {
     const DNode *nodes;       // internal nodes only
@@ -101,6 +111,7 @@ struct DScene {
     int n_meshes;
     const DTexture *textures;
     int n_textures;
+    const DFused *fused;      // material record float 14 = index into this table, or -1
     float cam_pos[3];
     float cam_axes[9];
     float cam_tan_half_fov[2];

@@ -68,7 +68,8 @@ void launch_resolve(const float *d_accum, size_t n_pixels, int samples, uint8_t 
 struct DRawMesh;
 struct NodeItem;
 struct BigLeafIndex;
-void launch_texture_quads(const DTexture &t, cudaStream_t st);   // fills t.quads from t.texels (rtb_assemble.cu)
+void launch_texture_quads(const DTexture &t, cudaStream_t st);
+void launch_fuse_textures(const DFused &f, const uchar4 *base, const uchar4 *mr, const uchar4 *nrm, cudaStream_t st);   // fills f.data   // fills t.quads from t.texels (rtb_assemble.cu)
 void launch_assemble_triangles(const DRawMesh *d_meshes, const uint32_t *d_mesh_first, int n_meshes, const uint32_t *d_tri_source, uint32_t n_tris,
                                float4 *d_tris, float4 *d_shade, float4 *d_tan, int *d_error, cudaStream_t stream);
 int launch_convert_nodes(uint32_t n_nodes, uint32_t n_internal, uint32_t n_tris, const float *d_aabb, const int32_t *d_links, const BigLeafIndex &big,

@@ -8,6 +8,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -157,6 +158,10 @@ struct HostLayout {
     int n_meshes = 0;
     bool any_normal_map = false;
     std::vector<float> lut;                 // DScene::lut
+    // DScene::fused: the textures of a material that share a size, interleaved per texel (rtb_device.cuh: DFused)
+    struct FusedGroup { int tex[3]; int width, height; };   // base colour, metallic-roughness, normal map (-1: none)
+    std::vector<FusedGroup> fused;
+    std::vector<char> texture_needs_quads;  // per texture: some use of it does not go through a fused record
 };
 
 // everything but the scene's own triangles and nodes: constants, light BVH (small, host-assembled), materials, textures
@@ -202,6 +207,39 @@ inline bool build_layout_common(const rtb_scene_desc *desc, HostLayout &L, std::
     for (uint32_t i = 0; i < desc->n_textures; ++i) {
         const rtb_texture_desc &t = desc->textures[i];
         if (t.width <= 0 || t.height <= 0 || !t.rgba) { err = "bad texture"; return false; }
+    }
+    // fused records: a material with at least two of {base colour, metallic-roughness, normal map}, all of one size;
+    // materials with the same three textures share a record (RTB_FUSE_TEXTURES=0: none -- every texture keeps its own quads)
+    L.fused.clear();
+    L.texture_needs_quads.assign(desc->n_textures, 0);
+    static const bool fuse_on = [] { const char *e = std::getenv("RTB_FUSE_TEXTURES"); return !(e && std::atoi(e) == 0); }();
+    for (int m = 0; m < L.n_meshes; ++m) {
+        float *mm = &mat[(size_t) m * 16];
+        const int t3[3] = {(int) mm[10], (int) mm[12], (int) mm[11]};   // base, metallic-roughness, normal
+        int present = 0, w = 0, h = 0;
+        bool same = true;
+        for (int k = 0; k < 3; ++k)
+            if (t3[k] >= 0) {
+                const rtb_texture_desc &t = desc->textures[t3[k]];
+                if (present && (t.width != w || t.height != h)) same = false;
+                w = t.width;
+                h = t.height;
+                ++present;
+            }
+        int id = -1;
+        if (fuse_on && present >= 2 && same) {
+            for (size_t g = 0; g < L.fused.size(); ++g)
+                if (L.fused[g].tex[0] == t3[0] && L.fused[g].tex[1] == t3[1] && L.fused[g].tex[2] == t3[2]) id = (int) g;
+            if (id < 0) {
+                id = (int) L.fused.size();
+                L.fused.push_back({{t3[0], t3[1], t3[2]}, w, h});
+            }
+        } else {
+            for (int k = 0; k < 3; ++k)
+                if (t3[k] >= 0) L.texture_needs_quads[(size_t) t3[k]] = 1;
+        }
+        if ((int) mm[13] >= 0) L.texture_needs_quads[(size_t) (int) mm[13]] = 1;   // emission
+        mm[14] = (float) id;
     }
     L.material.resize((size_t) L.n_meshes * 4);
     std::memcpy(L.material.data(), mat.data(), mat.size() * sizeof(float));

@@ -45,6 +45,19 @@ RTB_HD float dot(V3 a, V3 b) {            // vector.h:365-370: s = 0; s += a[i]*
 RTB_HD V3 cross(V3 a, V3 b) {             // vector.h:372-378
     return V3{a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y};
 }
+// The shade kernel is 72 KB of SASS of which 44 KB are hot, against a 32 KB L1.5 instruction cache: 21 % of its stall samples are
+// "no instruction" (profiles/r02h_sponza_k_wf_shade_summary.txt).  The helpers that were inlined at many sites are therefore
+// can be kept as ONE copy each in device code with -DRTB_SHADE_NOINLINE=1.  Measured on one box, A/B (profiles/
+// r02j_shade_noinline_ab.txt): the kernel shrinks 72 -> 66 KB, the calls cost more than the fetches they save -- shade
+// step 134 -> 144 ms per 64-spp frame.  Off.
+#ifndef RTB_SHADE_NOINLINE
+#define RTB_SHADE_NOINLINE 0
+#endif
+#if defined(__CUDA_ARCH__) && RTB_SHADE_NOINLINE
+#define RTB_HD_BIG __host__ __device__ __noinline__
+#else
+#define RTB_HD_BIG RTB_HD
+#endif
 RTB_HD float length(V3 v) {
     float m = 0.f;
     m = m + v.x * v.x;
@@ -52,7 +65,7 @@ RTB_HD float length(V3 v) {
     m = m + v.z * v.z;
     return sqrtf(m);
 }
-RTB_HD V3 normal(V3 v) {                  // vector.h:169-174
+RTB_HD_BIG V3 normal(V3 v) {                  // vector.h:169-174
     float mod = length(v);
     mod = 1.f / mod;
     return V3{v.x * mod, v.y * mod, v.z * mod};
@@ -258,9 +271,23 @@ RTB_HD int wrap_index(int i, int n) {   // i % n for 0 <= i <= n + 1
     return i >= n ? i - n : i;
 }
 RTB_HD uchar4 u2c(uint32_t v) { return make_uchar4((unsigned char) (v & 255u), (unsigned char) ((v >> 8) & 255u), (unsigned char) ((v >> 16) & 255u), (unsigned char) (v >> 24)); }
-template <bool SRGB>
-RTB_HD void texture_sample(const DScene &sc, int tex, float px, float py, float out[4]) {
+// where the quads of a texture use live: the material's fused record (slot k of 4 per texel) or the texture's own array
+struct TexView {
+    const uint4 *q;
+    int stride;       // uint4 per texel
+    int width, height;
+    const float *lut; // DScene::lut
+};
+RTB_HD TexView tex_view(const DScene &sc, int tex, int fused, int slot) {
+    if (fused >= 0) {
+        const DFused f = sc.fused[fused];
+        return TexView{f.data + slot, 4, f.width, f.height, sc.lut};
+    }
     const DTexture t = sc.textures[tex];
+    return TexView{t.quads, 1, t.width, t.height, sc.lut};
+}
+template <bool SRGB>
+RTB_HD_BIG void texture_sample(const TexView &t, float px, float py, float out[4]) {
     px = px - floorf(px);
     py = py - floorf(py);
     px = px * (float) t.width;
@@ -271,7 +298,7 @@ RTB_HD void texture_sample(const DScene &sc, int tex, float px, float py, float 
     // (x0 + 1) % width and (y0 + 1) % height ride in the quad of (x0, y0)
     const int x0 = wrap_index(ix, t.width);
     const int y0 = wrap_index(iy, t.height);
-    const uint4 q = ldg(&t.quads[(size_t) y0 * t.width + x0]);
+    const uint4 q = ldg(&t.q[((size_t) y0 * t.width + x0) * (size_t) t.stride]);
     const uchar4 c00 = u2c(q.x);   // (dx=0, dy=0)
     const uchar4 c01 = u2c(q.y);   // (dx=0, dy=1)
     const uchar4 c10 = u2c(q.z);   // (dx=1, dy=0)
@@ -282,9 +309,9 @@ RTB_HD void texture_sample(const DScene &sc, int tex, float px, float py, float 
     for (int i = 0; i < 3; ++i) {   // the alpha channel is never read by the hot path (.reduce())
         float a00, a01, a10, a11;
         if (SRGB) {
-            a00 = ldg(&sc.lut[b00[i]]); a01 = ldg(&sc.lut[b01[i]]); a10 = ldg(&sc.lut[b10[i]]); a11 = ldg(&sc.lut[b11[i]]);
+            a00 = ldg(&t.lut[b00[i]]); a01 = ldg(&t.lut[b01[i]]); a10 = ldg(&t.lut[b10[i]]); a11 = ldg(&t.lut[b11[i]]);
         } else {   // (float) byte / 255.f, tabulated
-            a00 = ldg(&sc.lut[256 + b00[i]]); a01 = ldg(&sc.lut[256 + b01[i]]); a10 = ldg(&sc.lut[256 + b10[i]]); a11 = ldg(&sc.lut[256 + b11[i]]);
+            a00 = ldg(&t.lut[256 + b00[i]]); a01 = ldg(&t.lut[256 + b01[i]]); a10 = ldg(&t.lut[256 + b10[i]]); a11 = ldg(&t.lut[256 + b11[i]]);
         }
         // interpolate_bilinear (primitive.h:158-161)
         out[i] = a00 * (1.f - dx) * (1.f - dy) + a01 * (1.f - dx) * dy + a10 * dx * (1.f - dy) + a11 * dx * dy;
@@ -297,6 +324,7 @@ struct Material {   // struct Material (primitive.h:76-89) as uploaded: 16 float
     V3 base, emission;
     float metallic, roughness2;
     int base_i, normal_i, mr_i, emission_i;
+    int fused;      // DScene::fused entry that holds base / metallic-roughness / normal map, or -1
 };
 RTB_HD Material load_material(const DScene &sc, int mesh) {
     const float4 *mp = sc.mesh_material + (size_t) mesh * 4;
@@ -307,6 +335,7 @@ RTB_HD Material load_material(const DScene &sc, int mesh) {
     m.emission = V3{b.y, b.z, b.w};
     m.metallic = c.x; m.roughness2 = c.y;
     m.base_i = (int) c.z; m.normal_i = (int) c.w; m.mr_i = (int) d.x; m.emission_i = (int) d.y;
+    m.fused = (int) d.z;
     return m;
 }
 
@@ -360,17 +389,18 @@ RTB_HD V3 shading_normal(const DScene &sc, int tri, const Shade &s, const Materi
     float tx, ty;
     texcoord(s, u, v, tx, ty);
     float smp[4];
-    texture_sample<false>(sc, m.normal_i, tx, ty, smp);
+    texture_sample<false>(tex_view(sc, m.normal_i, m.fused, kFusedNormal), tx, ty, smp);
     const V3 ln = V3{smp[0] + -0.5f, smp[1] + -0.5f, smp[2] + -0.5f} * 2.f;
     return normal((local_x * ln.x + local_y * ln.y) + local_z * ln.z);
 }
 // Primitive::get_color / get_emission (primitive.cpp:111-129)
-RTB_HD V3 textured_factor(const DScene &sc, const Shade &s, int tex, V3 factor, float u, float v) {
+// fused >= 0: the texture is slot kFusedBase of that fused record (the base colour); -1: its own quads (emission)
+RTB_HD V3 textured_factor(const DScene &sc, const Shade &s, int tex, int fused, V3 factor, float u, float v) {
     if (tex < 0) return factor;
     float tx, ty;
     texcoord(s, u, v, tx, ty);
     float smp[4];
-    texture_sample<true>(sc, tex, tx, ty, smp);
+    texture_sample<true>(tex_view(sc, tex, fused, kFusedBase), tx, ty, smp);
     return V3{smp[0], smp[1], smp[2]} * factor;
 }
 // Primitive::get_metallic_roughness (primitive.cpp:131-140) -> {roughness2, metallic}
@@ -383,7 +413,7 @@ RTB_HD void metallic_roughness(const DScene &sc, const Shade &s, const Material 
     float tx, ty;
     texcoord(s, u, v, tx, ty);
     float smp[4];
-    texture_sample<false>(sc, m.mr_i, tx, ty, smp);
+    texture_sample<false>(tex_view(sc, m.mr_i, m.fused, kFusedMR), tx, ty, smp);
     const float r2 = smp[1] * smp[1];
     rough2 = r2 * m.roughness2;
     metallic = smp[2] * m.metallic;
@@ -441,7 +471,7 @@ RTB_HD V3 trace_path(const DScene &sc, Ray r, Rng &g, PathCounters *pc) {
         const Material m = load_material(sc, s.mesh);
         Bounce &b = st[n];
         ++n;
-        b.emission = textured_factor(sc, s, m.emission_i, m.emission, h.u, h.v);
+        b.emission = textured_factor(sc, s, m.emission_i, -1, m.emission, h.u, h.v);
         b.coeff = 0.f;
         // the last vertex: its child is `power <= 0 -> return {}`; only the direction sample touches the stream
         const V3 pos = V3{r.o[0], r.o[1], r.o[2]} + rd * h.t;
@@ -464,7 +494,7 @@ RTB_HD V3 trace_path(const DScene &sc, Ray r, Rng &g, PathCounters *pc) {
         const float vis = smith_g(rough2, Ns, eye, dir) * (1.f / (4.f * fabsf(dot(Ns, rd)) * fabsf(dot(Ns, dir))));
         const float spec = ggx_d(rough2, Ns, half) * vis;
         const float VdotH = fabsf(dot(eye, half));
-        const V3 base = textured_factor(sc, s, m.base_i, m.base, h.u, h.v);
+        const V3 base = textured_factor(sc, s, m.base_i, m.fused, m.base, h.u, h.v);
         const float p5 = pow5_via_double(1.f - VdotH);
         const V3 metal = spec * V3{fresnel(base.x, p5), fresnel(base.y, p5), fresnel(base.z, p5)};
         const V3 diffuse = base * kInvPi;

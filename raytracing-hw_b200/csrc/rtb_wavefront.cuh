@@ -146,7 +146,7 @@ RTB_HD unsigned wf_shade_slot(const DScene &sc, const RenderLaunch &p, const WfS
         if (inside) Ng = -Ng;
         const Shade s = load_shade(sc, h.id);
         const Material m = load_material(sc, s.mesh);
-        const V3 emission = textured_factor(sc, s, m.emission_i, m.emission, h.u, h.v);
+        const V3 emission = textured_factor(sc, s, m.emission_i, -1, m.emission, h.u, h.v);
         last = emission;
         last_is_hit = true;
         const V3 pos = V3{r.o[0], r.o[1], r.o[2]} + rd * h.t;
@@ -169,7 +169,7 @@ RTB_HD unsigned wf_shade_slot(const DScene &sc, const RenderLaunch &p, const WfS
                 const float vis = smith_g(rough2, Ns, eye, dir) * (1.f / (4.f * fabsf(dot(Ns, rd)) * fabsf(dot(Ns, dir))));
                 const float spec = ggx_d(rough2, Ns, half) * vis;
                 const float VdotH = fabsf(dot(eye, half));
-                const V3 base = textured_factor(sc, s, m.base_i, m.base, h.u, h.v);
+                const V3 base = textured_factor(sc, s, m.base_i, m.fused, m.base, h.u, h.v);
                 const float p5 = pow5_via_double(1.f - VdotH);
                 const V3 metal = spec * V3{fresnel(base.x, p5), fresnel(base.y, p5), fresnel(base.z, p5)};
                 const V3 diffuse = base * kInvPi;

@@ -15,7 +15,8 @@ namespace {
 struct SimScene {
     HostLayout L;
     std::vector<DTexture> tex;
-    std::vector<std::vector<uint4>> quads;
+    std::vector<std::vector<uint4>> quads, fused_data;
+    std::vector<DFused> fused;
     DScene d;
 };
 
@@ -48,6 +49,17 @@ bool make_scene(const rtb_scene_desc *desc, SimScene &s, std::string &err) {
         s.tex[i] = {(const uchar4 *) desc->textures[i].rgba, s.quads[i].data(), w, h};
     }
     s.d.textures = s.tex.data();
+    s.fused.resize(s.L.fused.size());
+    s.fused_data.resize(s.L.fused.size());
+    for (size_t g = 0; g < s.L.fused.size(); ++g) {
+        const auto &G = s.L.fused[g];
+        auto px = [&](int ti) { return ti >= 0 ? (const uchar4 *) desc->textures[ti].rgba : nullptr; };
+        s.fused_data[g].resize((size_t) G.width * G.height * 4);
+        for (int y = 0; y < G.height; ++y)
+            for (int x = 0; x < G.width; ++x) fused_texel(px(G.tex[0]), px(G.tex[1]), px(G.tex[2]), G.width, G.height, x, y, &s.fused_data[g][((size_t) y * G.width + x) * 4]);
+        s.fused[g] = {s.fused_data[g].data(), G.width, G.height};
+    }
+    s.d.fused = s.fused.data();
     fill_scalars(desc, s.d);
     fill_lut(s.L.lut);
     s.d.lut = s.L.lut.data();
