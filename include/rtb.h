@@ -168,6 +168,18 @@ double rtb_host_scene_build_seconds(const rtb_host_scene *hs);
  * tests/test_gpu_build.py).  RTB_BUILD_GPU=0|1 forces the choice (default: scenes of >= 500 k triangles when a device exists),
  * RTB_BUILD_GPU_BELOW=<n> (default 5: the whole tree on the GPU) sets the node size below which the host carries on.                              */
 int rtb_host_scene_build_info(const rtb_host_scene *hs, double out8[8]);
+
+/* BVH::buildBVH alone (src/core/bvh.cpp:166-175; called from Scene::Scene, src/core/scene.cpp:213) for a caller that keeps
+ * its own scene: tri_pos9 = Primitive::position[0..2] of every triangle (p0, U = p1 - p0, V = p2 - p0; primitive.h:104,
+ * scene_parser.cpp:306-312), n of them, in the order of the caller's `primitives` vector.
+ *   order[i]            = index (into the caller's vector) of the triangle buildBVH leaves at position i
+ *   node_aabb/node_links = the reference's `nodes` in the reference's order: min xyz, max xyz / {left, right, split_dim,
+ *                         first_primitive_id, primitive_count}, -1 = invalidKey (src/core/bvh.h:8-17)
+ * node_capacity: nodes the two arrays hold (2 n - 1 always suffices); *n_nodes receives the count (RTB_ERR_INVALID and the
+ * needed count when the arrays are too small).  out8 (may be NULL): rtb_host_scene_build_info's record.  Runs on the GPU
+ * under the same policy as the scene loaders (RTB_BUILD_GPU), on the host otherwise; the layout is the reference's either way. */
+int rtb_build_bvh(const float *tri_pos9, size_t n, uint32_t *order, float *node_aabb, int32_t *node_links,
+                  size_t node_capacity, size_t *n_nodes, double out8[8]);
 void rtb_host_scene_destroy(rtb_host_scene *hs);
 
 /* ------------------------------------------------------------------------------------------------ device side */

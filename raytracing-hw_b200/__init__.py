@@ -24,7 +24,7 @@ REQUEST_COUNTERS = 0xFFFFFFFFFFFFFFFF
 ABI_SYMBOLS = [
     "rtb_last_error", "rtb_device_count",
     "rtb_host_scene_load_gltf", "rtb_host_scene_from_triangles", "rtb_host_scene_desc", "rtb_host_scene_bvh_stats",
-    "rtb_host_scene_build_seconds", "rtb_host_scene_build_info", "rtb_host_scene_destroy",
+    "rtb_host_scene_build_seconds", "rtb_host_scene_build_info", "rtb_build_bvh", "rtb_host_scene_destroy",
     "rtb_host_scene_raw_geometry", "rtb_scene_create_raw", "rtb_scene_read_buffer",
     "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_device", "rtb_scene_traversal_bytes", "rtb_scene_upload_bytes", "rtb_scene_launches", "rtb_scene_stage_ms",
     "rtb_closest_hit", "rtb_closest_hit_device", "rtb_light_pdf", "rtb_measure_l2",
@@ -114,6 +114,7 @@ def lib():
         L.rtb_host_scene_build_seconds.restype = C.c_double
         L.rtb_host_scene_build_seconds.argtypes = [C.c_void_p]
         L.rtb_host_scene_build_info.argtypes = [C.c_void_p, C.POINTER(C.c_double * 8)]
+        L.rtb_build_bvh.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_double * 8)]
         L.rtb_scene_traversal_bytes.restype = C.c_size_t
         L.rtb_scene_traversal_bytes.argtypes = [C.c_void_p]
         L.rtb_scene_upload_bytes.restype = C.c_size_t
@@ -177,6 +178,20 @@ def _ptr(a):
     if hasattr(a, "data_ptr"):      # torch tensor (host-pinned or device)
         return C.c_void_p(a.data_ptr())
     return C.c_void_p(int(a))
+
+
+def build_bvh(tri_pos9):
+    """BVH::buildBVH alone (rtb_build_bvh): tri_pos9 = (n, 9) float32 rows p0, U, V.  Returns (order, node_aabb, node_links, info)."""
+    pos = np.ascontiguousarray(tri_pos9, np.float32).reshape(-1, 9)
+    n = pos.shape[0]
+    cap = max(1, 2 * n - 1)
+    order = np.empty(n, np.uint32)
+    aabb = np.empty((cap, 6), np.float32)
+    links = np.empty((cap, 5), np.int32)
+    nn, o = C.c_size_t(0), (C.c_double * 8)()
+    _check(lib().rtb_build_bvh(_ptr(pos), n, _ptr(order), _ptr(aabb), _ptr(links), cap, C.byref(nn), C.byref(o)))
+    info = dict(on_gpu=bool(o[0]), levels=int(o[1]), rounds=int(o[2]), heap_ranges=int(o[3]), host_fallback_nodes=int(o[4]), gpu_seconds=o[5], kernel_seconds=o[6])
+    return order, aabb[:nn.value].copy(), links[:nn.value].copy(), info
 
 
 def device_count():

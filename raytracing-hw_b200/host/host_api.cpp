@@ -223,6 +223,39 @@ int rtb_host_scene_build_info(const rtb_host_scene *hs, double out8[8]) {
     return RTB_OK;
 }
 
+int rtb_build_bvh(const float *tri_pos9, size_t n, uint32_t *order, float *node_aabb, int32_t *node_links, size_t node_capacity,
+                  size_t *n_nodes, double out8[8]) {
+    if (!tri_pos9 || n == 0 || !order || !node_aabb || !node_links || !n_nodes) {
+        rtb::set_error("rtb_build_bvh: invalid argument");
+        return RTB_ERR_INVALID;
+    }
+    try {
+        rtb::HostTriangles t;
+        t.resize_core(n);
+        std::memcpy(t.pos.data(), tri_pos9, n * 9 * sizeof(float));
+        for (size_t i = 0; i < n; ++i) { t.mesh[i] = 0; t.source[i] = (uint32_t) i; }
+        rtb::HostBvh b;
+        rtb::build_bvh(t, b);
+        *n_nodes = b.size();
+        if (out8) {
+            const double o[8] = {b.built_on_gpu ? 1.0 : 0.0, (double) b.gpu.levels, (double) b.gpu.rounds, (double) b.gpu.heap_ranges,
+                                 (double) b.gpu.host_fallback_nodes, b.gpu.seconds, b.gpu.kernel_seconds, 0.0};
+            std::memcpy(out8, o, sizeof o);
+        }
+        if (b.size() > node_capacity) {
+            rtb::set_error("rtb_build_bvh: node arrays too small (" + std::to_string(b.size()) + " nodes)");
+            return RTB_ERR_INVALID;
+        }
+        std::memcpy(order, t.source.data(), n * sizeof(uint32_t));
+        std::memcpy(node_aabb, b.aabb.data(), b.aabb.size() * sizeof(float));
+        std::memcpy(node_links, b.links.data(), b.links.size() * sizeof(int32_t));
+        return RTB_OK;
+    } catch (const std::exception &e) {
+        rtb::set_error(std::string("rtb_build_bvh: ") + e.what());
+        return RTB_ERR_INVALID;
+    }
+}
+
 void rtb_host_scene_destroy(rtb_host_scene *hs) { delete hs; }
 
 int rtb_write_ppm(const char *path, int width, int height, const uint8_t *rgb8) {

@@ -102,3 +102,20 @@ def test_cfg3_one_million_default_path():
     host = build(tri, RTB_BUILD_GPU=0)
     same(host, gpu)
     print("1 M build: host %.3f s, GPU path %.3f s (%s)" % (host[4], gpu[4], gpu[3]))
+
+
+def test_build_bvh_entry_point_on_gpu():
+    """rtb_build_bvh, the drop-in for BVH::buildBVH alone: 600 k triangles go to the GPU builder by default; same answer as the host"""
+    tri = soup(600000, 8.4, seed=21)
+    pos = tri.copy()
+    pos[:, 3:6] = tri[:, 3:6] - tri[:, 0:3]
+    pos[:, 6:9] = tri[:, 6:9] - tri[:, 0:3]
+    o1, a1, l1, info = rtb.build_bvh(pos)
+    assert info["on_gpu"]
+    os.environ["RTB_BUILD_GPU"] = "0"
+    try:
+        o0, a0, l0, info0 = rtb.build_bvh(pos)
+    finally:
+        os.environ.pop("RTB_BUILD_GPU", None)
+    assert not info0["on_gpu"]
+    assert np.array_equal(o0, o1) and np.array_equal(l0, l1) and np.array_equal(a0.view(np.uint32), a1.view(np.uint32))

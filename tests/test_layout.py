@@ -122,3 +122,22 @@ def test_gltf_scene_equals_reference_fully(ref):
     cam, rcam = hs.camera(), rs.camera()
     assert np.array_equal(cam["pos"], rcam["pos"]) and np.array_equal(cam["axes"], rcam["axes"])
     assert cam["max_distance"] == rcam["max_distance"] and cam["ray_depth"] == rcam["ray_depth"] == 6
+
+
+def test_build_bvh_entry_point_equals_scene_build():
+    """rtb_build_bvh (BVH::buildBVH alone, for a caller that keeps its own scene): order, nodes and links equal what the scene
+    loaders build from the same triangles -- which the tests above pin against the reference"""
+    tri = _util.gen_scenes.soup_triangles(20000, seed=11, half_extent=2.7).reshape(-1, 9)
+    hs = _util.rtb.HostScene.from_triangles(tri)
+    loader_order = np.argsort(hs.tri_source())          # rows of tris()["pos"] back in the caller's order
+    pos_in = np.ascontiguousarray(hs.tris()["pos"])[loader_order]
+    order, aabb, links, info = _util.rtb.build_bvh(pos_in)
+    a, l = hs.nodes()
+    assert np.array_equal(order, hs.tri_source()) and np.array_equal(aabb.view(np.uint32), a.view(np.uint32)) and np.array_equal(links, l)
+    assert set(info) >= {"on_gpu", "levels", "rounds"}
+    with pytest.raises(_util.rtb.RtbError):
+        _util.rtb.lib().rtb_build_bvh  # (symbol present)
+        import ctypes as C
+        nn = C.c_size_t(0)
+        _util.rtb._check(_util.rtb.lib().rtb_build_bvh(_util.rtb._ptr(pos_in), pos_in.shape[0], _util.rtb._ptr(order), _util.rtb._ptr(aabb),
+                                                       _util.rtb._ptr(links), 3, C.byref(nn), None))   # arrays too small
