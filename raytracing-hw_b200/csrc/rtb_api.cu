@@ -74,6 +74,32 @@ struct BlockCache {
         }
         return e;
     }
+    // Frees are DEFERRED on threads that asked for it (defer_frees): a thread that renders one device of a multi-device frame
+    // must not call cudaFree -- it waits for a device to go idle, and a device whose NCCL kernel is waiting for THIS thread's
+    // rank never does (seen as a hang of rtb_render_multi on 8 GPUs when a scratch block grew while the cache was full and the
+    // oldest block belonged to another device).  The blocks go to `deferred` and are freed by flush_deferred() from a thread
+    // that holds no rank (rtb_render_multi after its threads have joined, scene creation / destruction).
+    std::vector<Block> deferred;
+    static bool &defer_flag() {
+        static thread_local bool f = false;
+        return f;
+    }
+    void free_now(std::vector<Block> &drop, int restore_device) {
+        for (const Block &b : drop) { cudaSetDevice(b.device); cudaFree(b.p); }
+        if (!drop.empty() && restore_device >= 0) cudaSetDevice(restore_device);
+        drop.clear();
+    }
+    void flush_deferred() {
+        std::vector<Block> drop;
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            drop.swap(deferred);
+        }
+        if (drop.empty()) return;
+        int cur = 0;
+        cudaGetDevice(&cur);
+        free_now(drop, cur);
+    }
     // the caller guarantees that no queued work uses the block any more
     void release(int device, void *p, size_t bytes) {
         if (!p) return;
@@ -84,15 +110,27 @@ struct BlockCache {
             else {
                 blocks.push_back(Block{device, p, bytes});
                 total += bytes;
-                while (total > limit() || blocks.size() > 8) {
-                    drop.push_back(blocks.front());
-                    total -= blocks.front().bytes;
-                    blocks.erase(blocks.begin());
-                }
+                // at most 8 blocks per device; over the byte limit the oldest blocks go, this device's first
+                auto count_dev = [&] { size_t c = 0; for (const Block &b : blocks) c += b.device == device; return c; };
+                auto drop_oldest = [&](bool same_device_only) {
+                    for (size_t i = 0; i < blocks.size(); ++i)
+                        if (!same_device_only || blocks[i].device == device) {
+                            drop.push_back(blocks[i]);
+                            total -= blocks[i].bytes;
+                            blocks.erase(blocks.begin() + (long) i);
+                            return true;
+                        }
+                    return false;
+                };
+                while (count_dev() > 8) drop_oldest(true);
+                while (total > limit() && (drop_oldest(true) || drop_oldest(false))) {}
+            }
+            if (defer_flag()) {
+                deferred.insert(deferred.end(), drop.begin(), drop.end());
+                drop.clear();
             }
         }
-        for (const Block &b : drop) { cudaSetDevice(b.device); cudaFree(b.p); }
-        if (!drop.empty()) cudaSetDevice(device);
+        free_now(drop, device);
     }
     void trim(int device) {   // device < 0: every device
         std::vector<Block> drop;
@@ -283,6 +321,9 @@ int ensure_stage(rtb_scene *sc, size_t bytes) {
 }  // namespace
 
 namespace rtb {
+// see BlockCache::release (rtb_dist.cu: the threads of rtb_render_multi)
+void blocks_defer_frees(bool on) { BlockCache::defer_flag() = on; }
+void blocks_flush_deferred() { g_blocks.flush_deferred(); }
 // device scratch block `which` (0..2) of a scene, at least `bytes` long (rtb_dist.cu)
 int scene_scratch(rtb_scene *sc, int which, size_t bytes, void **out) {
     if (sc->scratch_bytes[which] < bytes) {
@@ -913,7 +954,7 @@ int rtb_render_resume(rtb_scene *scene, const rtb_render_params *p, void *state,
     return RTB_OK;
 }
 
-void rtb_release_cached_memory(void) { rtb::g_blocks.trim(-1); }
+void rtb_release_cached_memory(void) { rtb::g_blocks.flush_deferred(); rtb::g_blocks.trim(-1); }
 
 unsigned long long rtb_scene_launches(const rtb_scene *scene) { return scene ? scene->launches : 0ull; }
 

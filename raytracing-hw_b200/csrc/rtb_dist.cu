@@ -19,6 +19,7 @@
 
 #include <dlfcn.h>
 #include <algorithm>
+#include <condition_variable>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -28,6 +29,8 @@
 namespace rtb {
 void set_error(const std::string &e);
 int scene_scratch(rtb_scene *sc, int which, size_t bytes, void **out);
+void blocks_defer_frees(bool on);
+void blocks_flush_deferred();
 cudaStream_t scene_stream(rtb_scene *sc);
 }  // namespace rtb
 
@@ -115,9 +118,35 @@ __global__ void __launch_bounds__(256) k_place_rows(const uint8_t *__restrict__ 
 
 }  // namespace
 
+// The ranks of ONE process (rtb_render_multi: a thread per device) meet here between "my part of the frame is rendered" and
+// the collective: a rank that failed before the collective would otherwise leave the others waiting in NCCL for ever.  Every
+// rank arrives with its status; all of them leave with the first failure (or RTB_OK) and enter the collective together or not
+// at all.  (Ranks in different processes have no such meeting point: a failed rank there ends its process.)
+struct MultiSync {
+    std::mutex m;
+    std::condition_variable cv;
+    int n = 0, arrived = 0, generation = 0, failed_rc = RTB_OK;
+    bool met[64] = {};            // rank r has been here (a rank that returns early is brought here by rtb_render_multi)
+    int arrive(int rank, int rc) {
+        std::unique_lock<std::mutex> lk(m);
+        met[rank] = true;
+        if (rc != RTB_OK && failed_rc == RTB_OK) failed_rc = rc;
+        const int gen = generation;
+        if (++arrived == n) {
+            arrived = 0;
+            ++generation;
+            cv.notify_all();
+        } else {
+            cv.wait(lk, [&] { return generation != gen; });
+        }
+        return failed_rc;
+    }
+};
+
 struct rtb_comm {
     ncclComm_p comm = nullptr;
     int world = 1, rank = 0, device = 0;
+    MultiSync *sync = nullptr;   // set by rtb_render_multi for the duration of a frame
 };
 
 extern "C" {
@@ -198,11 +227,18 @@ int rtb_render_dist_device(rtb_scene *scene, rtb_comm *comm, const rtb_render_pa
         const bool whole = p.substream_end - p.substream_begin == p.substreams;   // one rank holds every stream
         if (whole) return rtb_render_device(scene, &p, d_accum_root, d_rgb8_root, d_counters, stream_);
         void *local = nullptr, *total = nullptr;
-        if ((rc = rtb::scene_scratch(scene, 0, W * H * 3 * sizeof(float), &local)) != RTB_OK) return rc;
-        if ((rc = rtb_render_device(scene, &p, (float *) local, nullptr, d_counters, stream_)) != RTB_OK) return rc;
-        if (rank == 0) {
+        rc = rtb::scene_scratch(scene, 0, W * H * 3 * sizeof(float), &local);
+        if (rc == RTB_OK) rc = rtb_render_device(scene, &p, (float *) local, nullptr, d_counters, stream_);
+        if (rc == RTB_OK && rank == 0) {
             total = d_accum_root;
-            if (!total && (rc = rtb::scene_scratch(scene, 1, W * H * 3 * sizeof(float), &total)) != RTB_OK) return rc;
+            if (!total) rc = rtb::scene_scratch(scene, 1, W * H * 3 * sizeof(float), &total);
+        }
+        if (comm && comm->sync) {   // all ranks of this process enter the collective, or none
+            const int all = comm->sync->arrive(rank, rc);
+            if (rc == RTB_OK && all != RTB_OK) rtb::set_error("rtb_render_dist_device: another rank of the frame failed");
+            if (all != RTB_OK) return rc != RTB_OK ? rc : all;
+        } else if (rc != RTB_OK) {
+            return rc;
         }
         RTB_NCCL(a->Reduce(local, total, W * H * 3, kNcclFloat32, kNcclSum, 0, comm->comm, stream));
         if (rank == 0 && d_rgb8_root) rtb::launch_resolve((const float *) total, W * H, frame->samples, d_rgb8_root, stream);
@@ -229,10 +265,19 @@ int rtb_render_dist_device(rtb_scene *scene, rtb_comm *comm, const rtb_render_pa
     void *local = nullptr, *side = nullptr;
     if (rank == 0) {
         // rank 0 renders straight into its place in the side-by-side buffer (offset 0)
-        if ((rc = rtb::scene_scratch(scene, 1, (size_t) off * W * 3 + 256, &side)) != RTB_OK) return rc;
+        rc = rtb::scene_scratch(scene, 1, (size_t) off * W * 3 + 256, &side);
         local = side;
-    } else if ((rc = rtb::scene_scratch(scene, 0, (size_t) local_rows * W * 3 + 256, &local)) != RTB_OK) return rc;
-    if ((rc = rtb_render_device(scene, &p, nullptr, (uint8_t *) local, d_counters, stream_)) != RTB_OK) return rc;
+    } else {
+        rc = rtb::scene_scratch(scene, 0, (size_t) local_rows * W * 3 + 256, &local);
+    }
+    if (rc == RTB_OK) rc = rtb_render_device(scene, &p, nullptr, (uint8_t *) local, d_counters, stream_);
+    if (comm && comm->sync) {   // all ranks of this process enter the collective, or none
+        const int all = comm->sync->arrive(rank, rc);
+        if (rc == RTB_OK && all != RTB_OK) rtb::set_error("rtb_render_dist_device: another rank of the frame failed");
+        if (all != RTB_OK) return rc != RTB_OK ? rc : all;
+    } else if (rc != RTB_OK) {
+        return rc;
+    }
     RTB_NCCL(a->GroupStart());
     if (rank == 0) {
         for (int r = 1; r < world; ++r)
@@ -314,21 +359,29 @@ int rtb_render_multi(rtb_scene *const *scenes, int n, const rtb_render_params *f
         if (rc != RTB_OK) return rc;
         fresh.assign((size_t) n, nullptr);
     }
+    MultiSync sync;
+    sync.n = n;
     std::vector<std::thread> th;
     for (int r = 0; r < n; ++r) {
         th.emplace_back([&, r] {
+            rtb::blocks_defer_frees(true);   // no cudaFree on a thread that holds a rank (BlockCache::release)
             int e = RTB_OK;
             rtb_comm *c = comms ? (*comms)[(size_t) r] : nullptr;
             if (!comms) {
                 e = rtb_comm_create(id, n, r, devs[(size_t) r], &c);
                 fresh[(size_t) r] = c;
             }
+            // (a rank without a communicator cannot take part: it still has to be counted at the meeting point)
+            if (c) c->sync = &sync;
             if (e == RTB_OK) e = rtb_render_dist(scenes[r], c, frame, split, r == 0 ? rgb8 : nullptr, &st[(size_t) r]);
+            if (!sync.met[r]) sync.arrive(r, e);   // returned before the meeting point: the others must not wait
+            if (c) c->sync = nullptr;
             if (e != RTB_OK) errs[(size_t) r] = rtb_last_error();
             rcs[(size_t) r] = e;
         });
     }
     for (auto &t : th) t.join();
+    rtb::blocks_flush_deferred();
     if (!comms) {
         bool all = true;
         for (auto *c : fresh) all = all && c != nullptr;

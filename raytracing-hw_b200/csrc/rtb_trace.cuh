@@ -40,6 +40,12 @@
 #ifndef RTB_TRACE_STATE_CS
 #define RTB_TRACE_STATE_CS 0
 #endif
+//   RTB_FETCH_HINTS      : L1 policy of the record fetch by kind -- 1: triangle records do not allocate in the L1 (a scene's triangles
+//                          are far more than an L1 holds and are rarely fetched twice by the same SM; the nodes near the root are
+//                          fetched by every ray), 2: the same and node records with evict_last
+#ifndef RTB_FETCH_HINTS
+#define RTB_FETCH_HINTS 0
+#endif
 
 namespace rtb {
 
@@ -386,6 +392,26 @@ __device__ __forceinline__ void ldg256(const float4 *p, float4 &lo, int4 &hi) {
                  : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=r"(hi.x), "=r"(hi.y), "=r"(hi.z), "=r"(hi.w)
                  : "l"(p));
 }
+__device__ __forceinline__ void ldg256_noalloc(const float4 *p, float4 &lo, float4 &hi) {
+    asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w)
+                 : "l"(p));
+}
+__device__ __forceinline__ void ldg256_noalloc(const float4 *p, float4 &lo, int4 &hi) {
+    asm volatile("ld.global.nc.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=r"(hi.x), "=r"(hi.y), "=r"(hi.z), "=r"(hi.w)
+                 : "l"(p));
+}
+__device__ __forceinline__ void ldg256_last(const float4 *p, float4 &lo, float4 &hi) {
+    asm volatile("ld.global.nc.L1::evict_last.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w)
+                 : "l"(p));
+}
+__device__ __forceinline__ void ldg256_last(const float4 *p, float4 &lo, int4 &hi) {
+    asm volatile("ld.global.nc.L1::evict_last.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=r"(hi.x), "=r"(hi.y), "=r"(hi.z), "=r"(hi.w)
+                 : "l"(p));
+}
 // The persistent loop of the queue kernels ("form 3", see LaneTraversal::pre3); MODE - 2 steps are taken between two
 // refill votes (MODE 3 / 4 / 5).  Earlier forms -- one phase per warp iteration chosen by vote; the first unified step
 // with the pop and the leaf decode inlined at three sites -- and what was tried and dropped (parked leaves, batching or
@@ -461,8 +487,23 @@ __device__ __forceinline__ void trace_persistent(const DBvh &b, unsigned n, unsi
             const float4 *p = doN ? reinterpret_cast<const float4 *>(b.nodes + L.link) : (b.tris + (size_t) (doL ? L.link & 0x0FFFFFFF : 0) * kTriStride);
             float4 a, bb, c;
             int4 d;
+#if RTB_FETCH_HINTS
+            if (doN) {
+#if RTB_FETCH_HINTS >= 2
+                ldg256_last(p, a, bb);
+                ldg256_last(p + 2, c, d);
+#else
+                ldg256(p, a, bb);
+                ldg256(p + 2, c, d);
+#endif
+            } else {
+                ldg256_noalloc(p, a, bb);
+                ldg256_noalloc(p + 2, c, d);
+            }
+#else
             ldg256(p, a, bb);
             ldg256(p + 2, c, d);
+#endif
 #if RTB_PREFETCH_LEAF
             // the next triangle of the leaf (if any) will be fetched by this lane's next step whatever this test says
             if (doL && (unsigned) (L.link - 0x0FFFFFFF) >= LaneTraversal<COUNT, RING>::kLeafBusy) prefetch_l1(p + kTriStride);

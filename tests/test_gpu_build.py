@@ -119,3 +119,29 @@ def test_build_bvh_entry_point_on_gpu():
         os.environ.pop("RTB_BUILD_GPU", None)
     assert not info0["on_gpu"]
     assert np.array_equal(o0, o1) and np.array_equal(l0, l1) and np.array_equal(a0.view(np.uint32), a1.view(np.uint32))
+
+
+def test_cfg5_scene_equals_host():
+    """BASELINE cfg5's scene (10 M-triangle soup + the emissive triangle, through the glTF loader): the GPU build -- which meets
+    introsort ranges that run out of depth here and heap-sorts them -- equals the host build, nodes (bits), links, triangle order"""
+    p = _util.scene_path("soup_10m")
+    os.environ["RTB_BUILD_GPU"] = "1"
+    try:
+        g = rtb.HostScene.load_gltf(p, 64, 64, 1)
+        gi = g.build_info()
+        ga, gl = g.nodes()
+        gs = g.tri_source().copy()
+        import hashlib
+        gd = (hashlib.sha256(ga.tobytes()).hexdigest(), hashlib.sha256(gl.tobytes()).hexdigest())
+        gsec = g.build_seconds
+        del g, ga, gl
+        os.environ["RTB_BUILD_GPU"] = "0"
+        h = rtb.HostScene.load_gltf(p, 64, 64, 1)
+        ha, hl = h.nodes()
+        hd = (hashlib.sha256(ha.tobytes()).hexdigest(), hashlib.sha256(hl.tobytes()).hexdigest())
+        assert gi["on_gpu"] and not h.build_info()["on_gpu"]
+        assert np.array_equal(gs, h.tri_source()), "triangle order differs"
+        assert gd == hd, "nodes differ"
+        print("cfg5 build: host %.2f s, GPU path %.2f s, %s" % (h.build_seconds, gsec, gi))
+    finally:
+        os.environ.pop("RTB_BUILD_GPU", None)
