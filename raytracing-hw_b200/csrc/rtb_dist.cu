@@ -16,10 +16,10 @@
 // else the system's), so librtb.so itself links nothing but the CUDA runtime.
 #include "../../include/rtb.h"
 #include "rtb_kernels.cuh"
+#include "rtb_multisync.h"
 
 #include <dlfcn.h>
 #include <algorithm>
-#include <condition_variable>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -117,31 +117,6 @@ __global__ void __launch_bounds__(256) k_place_rows(const uint8_t *__restrict__ 
 }
 
 }  // namespace
-
-// The ranks of ONE process (rtb_render_multi: a thread per device) meet here between "my part of the frame is rendered" and
-// the collective: a rank that failed before the collective would otherwise leave the others waiting in NCCL for ever.  Every
-// rank arrives with its status; all of them leave with the first failure (or RTB_OK) and enter the collective together or not
-// at all.  (Ranks in different processes have no such meeting point: a failed rank there ends its process.)
-struct MultiSync {
-    std::mutex m;
-    std::condition_variable cv;
-    int n = 0, arrived = 0, generation = 0, failed_rc = RTB_OK;
-    bool met[64] = {};            // rank r has been here (a rank that returns early is brought here by rtb_render_multi)
-    int arrive(int rank, int rc) {
-        std::unique_lock<std::mutex> lk(m);
-        met[rank] = true;
-        if (rc != RTB_OK && failed_rc == RTB_OK) failed_rc = rc;
-        const int gen = generation;
-        if (++arrived == n) {
-            arrived = 0;
-            ++generation;
-            cv.notify_all();
-        } else {
-            cv.wait(lk, [&] { return generation != gen; });
-        }
-        return failed_rc;
-    }
-};
 
 struct rtb_comm {
     ncclComm_p comm = nullptr;

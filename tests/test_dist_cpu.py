@@ -103,3 +103,16 @@ def test_rank_rows_partition():
             assert [(_util.rtb.lib().rtb_render_global_row(C.byref(p), i)) for i in range(0, n, 37)] == list(rows[::37])
             seen += list(rows)
         assert sorted(seen) == list(range(1080))
+
+
+def test_rank_threads_meet_before_the_collective():
+    """rtb_render_multi's rank threads (one process, a thread per GPU) meet before the NCCL step: all leave with the first
+    failure of the frame or with success, and a rank that failed before the meeting point does not leave the others waiting
+    (csrc/rtb_multisync.h, driven by threads on the host)"""
+    import os
+    import subprocess
+    import _util
+    exe = os.path.join(_util.ROOT, "tests", "devsim", "multisync_check")
+    subprocess.run(["make", "-C", os.path.dirname(exe), "multisync_check"], check=True, stdout=subprocess.DEVNULL)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout
