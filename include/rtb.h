@@ -246,8 +246,9 @@ size_t rtb_scene_traversal_bytes(const rtb_scene *scene);
 size_t rtb_scene_upload_bytes(const rtb_scene *scene);
 
 /* Device blocks of destroyed scenes (scene arena, path state, staging buffers) are kept for the next scene -- at most
- * 8 blocks / RTB_BLOCK_CACHE_MB megabytes (default 8192; 0 = none) per process -- so that re-creating a scene per frame
- * does not pay cudaMalloc / cudaFree of ~1 GB each time.  This call hands all of them back to the driver.             */
+ * 8 blocks per device and RTB_BLOCK_CACHE_MB megabytes (default 8192; 0 = none) per process -- so that re-creating a scene
+ * per frame does not pay cudaMalloc / cudaFree of ~1 GB each time.  This call hands all of them back to the driver.
+ * (The threads of rtb_render_multi never free: what they drop is freed when the call returns.)                          */
 void rtb_release_cached_memory(void);
 /* kernels launched so far by rtb_render / rtb_render_device calls on this scene */
 unsigned long long rtb_scene_launches(const rtb_scene *scene);
