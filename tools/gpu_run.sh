@@ -2,7 +2,8 @@
 # The one GPU-box runner (replaces the per-experiment scripts of round 1):  tools/gpu_run.sh <tag> <stage> [<stage> ...]
 # Every stage writes gpurun_out/<tag>_<stage>.{log,json,csv}; nothing here is timed under a profiler except the ncu stages.
 # Stages:  tests | tests_quick | smoke | bench | bench_short | bench_s7_4 | bench_soup10m | closest_hit | launches | ncu_trace |
-#          ncu_shade | ncu_soup10m | ncu_s7_4 | ncu_frame | variants (needs VARIANTS="a.so b.so", SPP) | multi (needs NGPU) | scale (needs NGPU)
+#          ncu_shade | ncu_soup10m | ncu_s7_4 | ncu_frame | variants (needs VARIANTS="a.so b.so", SPP) | multi (needs NGPU) | scale (needs NGPU) |
+#          build_time (host / GPU builder at 1 M and 10 M) | coherence (ray ordering experiment) | ab_fuse (fused texel records on / off)
 set -u
 TAG=$1; shift
 OUT=gpurun_out; mkdir -p $OUT
@@ -49,6 +50,9 @@ for stage in "$@"; do
                     trun $NGPU bench.py --gpus $NGPU --steps ${STEPS:-3} --warmup 3 --split $split > $OUT/${TAG}_bench_n${NGPU}_$split.json 2> $OUT/${TAG}_bench_n${NGPU}_$split.err; cut -c1-300 $OUT/${TAG}_bench_n${NGPU}_$split.json
                   done ;;
     scale_soup10m) SP=${SPLIT:-sample}; trun $NGPU bench.py --gpus $NGPU --workload soup_10m --steps ${STEPS:-3} --warmup 3 --split $SP > $OUT/${TAG}_bench_soup10m_n${NGPU}_$SP.json 2> $OUT/${TAG}_bench_soup10m_n${NGPU}_$SP.err; cut -c1-300 $OUT/${TAG}_bench_soup10m_n${NGPU}_$SP.json ;;
+    build_time)   timeout 900 $PY tools/build_time.py > $OUT/${TAG}_build_time.jsonl 2> $OUT/${TAG}_build_time.err; cut -c1-200 $OUT/${TAG}_build_time.jsonl ;;
+    coherence)    timeout 600 $PY tools/exp_ray_coherence.py > $OUT/${TAG}_ray_coherence.jsonl 2> $OUT/${TAG}_ray_coherence.err; cut -c1-200 $OUT/${TAG}_ray_coherence.jsonl ;;
+    ab_fuse)      tools/ab_fuse.sh > $OUT/${TAG}_fuse_ab.txt 2>&1; cat $OUT/${TAG}_fuse_ab.txt ;;
     *) echo "unknown stage $stage" ;;
   esac
 done
