@@ -19,7 +19,11 @@
 // std::partition on z is replayed on the host) are returned as ranges of the order array for the host builder.
 #include "rtb_build.h"
 
+#ifdef RTB_BUILD_EMULATE   // tests/devsim/build_emul: this file compiled for the host, kernels run as loops (test tooling)
+#include "cuda_emulation.h"
+#else
 #include <cuda_runtime.h>
+#endif
 
 #include <algorithm>
 #include <chrono>
@@ -51,6 +55,7 @@ struct SumOp {
     __device__ __forceinline__ unsigned long long operator()(unsigned long long a, unsigned long long b) const { return a + b; }
 };
 
+#ifndef RTB_BUILD_EMULATE
 // ---- inclusive scan with an associative (not necessarily commutative) operator, three passes
 template <class T, class Op>
 __global__ void __launch_bounds__(kScanThreads) k_scan_tiles(const T *in, T *out, T *__restrict__ agg, uint32_t n, Op op) {
@@ -134,6 +139,20 @@ void scan_inclusive(const T *in, T *out, T *agg, uint32_t n, Op op, cudaStream_t
         k_scan_apply<T, Op><<<tiles, kScanThreads, 0, st>>>(out, agg, n, op);
     }
 }
+
+#else
+// (host emulation: threads of a block run one after the other, so the block-wide scans above cannot; same operator, in order)
+template <class T, class Op>
+void scan_inclusive(const T *in, T *out, T *, uint32_t n, Op op, cudaStream_t) {
+    if (n == 0) return;
+    T acc = in[0];
+    out[0] = acc;
+    for (uint32_t i = 1; i < n; ++i) {
+        acc = op(acc, in[i]);
+        out[i] = acc;
+    }
+}
+#endif
 
 // ---- a level of the tree
 struct LevelNode {

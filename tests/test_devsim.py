@@ -225,6 +225,20 @@ def test_gpu_builder_sort_replay_equals_std_sort():
     assert r.returncode == 0 and r.stdout.startswith("ok"), r.stdout
 
 
+def test_gpu_builder_source_emulated_on_the_host_equals_host_builder():
+    """csrc/rtb_build.cu itself -- kernels and level loop, the source the B200 runs -- compiled for the host (tests/devsim/emul:
+    a launch runs its threads one after the other over host memory) against the host builder behind rtb_build_bvh: node boxes
+    (bits), links, split axes, triangle order, on random / quantised / duplicated soups, a flat axis-aligned grid with zeros of
+    both signs, coincident triangles (no cut improves: std::partition on z in the node's thread; handed back above 256), tiny
+    scenes and forced depth limits (heap-sorted ranges)"""
+    import os
+    import subprocess
+    d = os.path.join(_util.ROOT, "tests", "devsim")
+    subprocess.run(["make", "-C", d, "build_emul_check"], check=True, stdout=subprocess.DEVNULL)
+    r = subprocess.run([os.path.join(d, "build_emul_check")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok") and "FAILED" not in r.stdout, r.stdout[-3000:]
+
+
 def _big_leaf_scene():
     """40 + 9 coincident triangles (their centroids cannot be split: leaves of 40 and 9 triangles, and every ray that hits
     them produces exact ties, which the first triangle in the reference's order must win) among 300 random ones"""
