@@ -23,12 +23,14 @@ enum { cudaSuccess = 0 };
 enum { cudaMemcpyHostToDevice = 1, cudaMemcpyDeviceToHost = 2, cudaMemcpyDeviceToDevice = 3 };
 enum { cudaStreamNonBlocking = 1 };
 inline cudaError_t cudaGetDeviceCount(int *n) { *n = 1; return cudaSuccess; }
-inline cudaError_t cudaGetDevice(int *d) { *d = 0; return cudaSuccess; }
-inline cudaError_t cudaSetDevice(int) { return cudaSuccess; }
+inline int emu_device = 0;                 // per process (the tests that look at it are single-threaded there)
+inline int emu_frees[64] = {};             // cudaFree calls by current device
+inline cudaError_t cudaGetDevice(int *d) { *d = emu_device; return cudaSuccess; }
+inline cudaError_t cudaSetDevice(int d) { emu_device = d; return cudaSuccess; }
 inline cudaError_t cudaGetLastError() { return cudaSuccess; }
 inline const char *cudaGetErrorString(cudaError_t) { return "emulated"; }
 inline cudaError_t cudaMalloc(void **p, size_t bytes) { *p = std::malloc(bytes); return *p ? cudaSuccess : 2; }
-inline cudaError_t cudaFree(void *p) { std::free(p); return cudaSuccess; }
+inline cudaError_t cudaFree(void *p) { if (p) ++emu_frees[emu_device & 63]; std::free(p); return cudaSuccess; }
 inline cudaError_t cudaMemcpyAsync(void *dst, const void *src, size_t bytes, int, cudaStream_t) { std::memcpy(dst, src, bytes); return cudaSuccess; }
 inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
 inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t *s, int) { *s = nullptr; return cudaSuccess; }

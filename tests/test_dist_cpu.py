@@ -116,3 +116,16 @@ def test_rank_threads_meet_before_the_collective():
     subprocess.run(["make", "-C", os.path.dirname(exe), "multisync_check"], check=True, stdout=subprocess.DEVNULL)
     r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout
+
+
+def test_block_cache_never_frees_on_a_rank_thread():
+    """librtb's block cache (csrc/rtb_block_cache.h) on the host: reuse rule, per-device block limit, byte limit, and the
+    deferred frees of rtb_render_multi's rank threads (a cudaFree there can wait for a device whose NCCL kernel waits for
+    the freeing rank)"""
+    import os
+    import subprocess
+    import _util
+    exe = os.path.join(_util.ROOT, "tests", "devsim", "block_cache_check")
+    subprocess.run(["make", "-C", os.path.dirname(exe), "block_cache_check"], check=True, stdout=subprocess.DEVNULL)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout
