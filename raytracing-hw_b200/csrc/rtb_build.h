@@ -38,4 +38,11 @@ struct GpuBuildStats {
 bool gpu_build_top(const float *tbox, const float *tcenter, size_t n, size_t host_below, int device, int depth_override,
                    std::vector<GpuTopNode> &nodes, std::vector<uint32_t> &order, GpuBuildStats &stats, std::string &err);
 
+// Test hook (tests/devsim/build_emul_check): the function the host builder calls for the GPU part -- null restores the real one.
+// Lets the hand-over between the two builders (host/bvh_builder.cpp: adopt_all) run in a container without a GPU, against the
+// builder's own source compiled for the host.
+using GpuBuildFn = bool (*)(const float *, const float *, size_t, size_t, int, int, std::vector<GpuTopNode> &, std::vector<uint32_t> &,
+                            GpuBuildStats &, std::string &);
+void set_gpu_builder_for_tests(GpuBuildFn fn);
+
 }  // namespace rtb

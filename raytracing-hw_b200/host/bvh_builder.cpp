@@ -30,6 +30,10 @@
 
 namespace rtb {
 namespace {
+GpuBuildFn g_gpu_build = &gpu_build_top;
+}
+void set_gpu_builder_for_tests(GpuBuildFn fn) { g_gpu_build = fn ? fn : &gpu_build_top; }
+namespace {
 
 // Large work arrays are first touched right after they are allocated; with 4 KB pages that is ~100 k page faults per array
 // at 10 M triangles (0.1 - 0.5 s each, and they serialise across threads).  Ask for transparent huge pages on the part of
@@ -505,7 +509,7 @@ void build_bvh(HostTriangles &tris, HostBvh &out, int threads) {
             std::vector<uint32_t> ord;
             GpuBuildStats gs;
             std::string err;
-            if (gpu_build_top(reinterpret_cast<const float *>(B.tbox.data()), B.tcenter.data(), n, below, -1, sort_depth_override(), top, ord, gs, err)) {
+            if (g_gpu_build(reinterpret_cast<const float *>(B.tbox.data()), B.tcenter.data(), n, below, -1, sort_depth_override(), top, ord, gs, err)) {
                 B.order.swap(ord);
                 out.gpu = gs;
                 out.built_on_gpu = true;

@@ -5,9 +5,10 @@
 // or do not reach: degenerate geometry (coincident triangles, flat axis-aligned grids with zeros of both signs), nodes no cut
 // improves (std::partition on z replayed in the node's thread; handed back above 256 triangles), tiny scenes, forced depth limits.
 #define RTB_BUILD_EMULATE 1
-#define rtb rtb_emul
+#define gpu_build_top gpu_build_top_emulated   // (librtb.so has the real one; this is rtb::gpu_build_top_emulated)
 #include "build_emul_gen.inc"
-#undef rtb
+#undef gpu_build_top
+namespace rtb_emul = rtb;
 
 #include <cstdio>
 #include <limits>
@@ -78,7 +79,7 @@ static int check(const char *what, const std::vector<float> &pos, int depth_over
     std::vector<uint32_t> order;
     rtb_emul::GpuBuildStats gs;
     std::string err;
-    if (!rtb_emul::gpu_build_top(tbox.data(), ctr.data(), n, 5, 0, depth_override, top, order, gs, err)) {
+    if (!rtb::gpu_build_top_emulated(tbox.data(), ctr.data(), n, 5, 0, depth_override, top, order, gs, err)) {
         std::printf("FAILED %s: emulated builder: %s\n", what, err.c_str());
         return 1;
     }
@@ -169,6 +170,31 @@ int main() {
         bad |= check("sorted along x", p, -1);
     }
     for (int d : {0, 2, 5}) bad |= check(d == 0 ? "depth limit 0 (everything heap-sorted)" : "depth limit cut (heap-sorted ranges)", soup(12000, 2.5f, d == 5 ? 6.f : 0.f), d);
+    // ---- the hand-over between the two builders (host/bvh_builder.cpp: adopt_all) with the emulated builder in the GPU's place:
+    // rtb_build_bvh under RTB_BUILD_GPU=1 and several hand-over sizes against the host build
+    rtb::set_gpu_builder_for_tests(&rtb::gpu_build_top_emulated);
+    unsetenv("RTB_BUILD_SORT_DEPTH");
+    for (size_t n : {300u, 5000u, 60000u}) {
+        const std::vector<float> pos = soup(n, 3.f, n == 5000u ? 4.f : 0.f);
+        std::vector<uint32_t> o0(n), o1(n);
+        std::vector<float> a0(2 * n * 6), a1(2 * n * 6);
+        std::vector<int32_t> l0(2 * n * 5), l1(2 * n * 5);
+        size_t n0 = 0, n1 = 0;
+        setenv("RTB_BUILD_GPU", "0", 1);
+        int rc = rtb_build_bvh(pos.data(), n, o0.data(), a0.data(), l0.data(), 2 * n, &n0, nullptr);
+        for (const char *below : {"5", "64", "512"}) {
+            setenv("RTB_BUILD_GPU", "1", 1);
+            setenv("RTB_BUILD_GPU_BELOW", below, 1);
+            double info[8] = {0};
+            rc |= rtb_build_bvh(pos.data(), n, o1.data(), a1.data(), l1.data(), 2 * n, &n1, info);
+            const bool used = info[0] == 1.0 || n < (size_t) std::atoi(below);
+            const bool same = rc == 0 && n0 == n1 && std::memcmp(o0.data(), o1.data(), n * 4) == 0 && std::memcmp(l0.data(), l1.data(), n0 * 20) == 0 &&
+                              std::memcmp(a0.data(), a1.data(), n0 * 24) == 0;
+            std::printf("%s  hand-over below %-4s %38s %8zu triangles %8zu nodes\n", same && used ? "ok" : "FAILED", below, "", n, n1);
+            if (!same || !used) bad = 1;
+        }
+    }
+    rtb::set_gpu_builder_for_tests(nullptr);
     std::printf("%s\n", bad ? "FAILED" : "ok");
     return bad;
 }

@@ -230,7 +230,8 @@ def test_gpu_builder_source_emulated_on_the_host_equals_host_builder():
     a launch runs its threads one after the other over host memory) against the host builder behind rtb_build_bvh: node boxes
     (bits), links, split axes, triangle order, on random / quantised / duplicated soups, a flat axis-aligned grid with zeros of
     both signs, coincident triangles (no cut improves: std::partition on z in the node's thread; handed back above 256), tiny
-    scenes and forced depth limits (heap-sorted ranges)"""
+    scenes and forced depth limits (heap-sorted ranges); then the hand-over between the two builders (host/bvh_builder.cpp:
+    adopt_all) with the emulated builder in the GPU's place, hand-over sizes 5 / 64 / 512"""
     import os
     import subprocess
     d = os.path.join(_util.ROOT, "tests", "devsim")
