@@ -23,14 +23,28 @@ enum { cudaSuccess = 0 };
 enum { cudaMemcpyHostToDevice = 1, cudaMemcpyDeviceToHost = 2, cudaMemcpyDeviceToDevice = 3 };
 enum { cudaStreamNonBlocking = 1 };
 inline cudaError_t cudaGetDeviceCount(int *n) { *n = 1; return cudaSuccess; }
-inline int emu_device = 0;                 // per process (the tests that look at it are single-threaded there)
+inline thread_local int emu_device = 0;    // the current device is per thread, as in CUDA
 inline int emu_frees[64] = {};             // cudaFree calls by current device
+inline void (*emu_free_hook)() = nullptr;  // called by every cudaFree of a non-null pointer (tests: who frees, and when)
 inline cudaError_t cudaGetDevice(int *d) { *d = emu_device; return cudaSuccess; }
 inline cudaError_t cudaSetDevice(int d) { emu_device = d; return cudaSuccess; }
 inline cudaError_t cudaGetLastError() { return cudaSuccess; }
 inline const char *cudaGetErrorString(cudaError_t) { return "emulated"; }
 inline cudaError_t cudaMalloc(void **p, size_t bytes) { *p = std::malloc(bytes); return *p ? cudaSuccess : 2; }
-inline cudaError_t cudaFree(void *p) { if (p) ++emu_frees[emu_device & 63]; std::free(p); return cudaSuccess; }
+inline cudaError_t cudaFree(void *p) {
+    if (p) {
+        __sync_fetch_and_add(&emu_frees[emu_device & 63], 1);
+        if (emu_free_hook) emu_free_hook();
+    }
+    std::free(p);
+    return cudaSuccess;
+}
+inline cudaError_t cudaMemsetAsync(void *p, int v, size_t bytes, cudaStream_t) { std::memset(p, v, bytes); return cudaSuccess; }
+typedef void *cudaEvent_t;
+inline cudaError_t cudaEventCreate(cudaEvent_t *e) { *e = nullptr; return cudaSuccess; }
+inline cudaError_t cudaEventRecord(cudaEvent_t, cudaStream_t) { return cudaSuccess; }
+inline cudaError_t cudaEventDestroy(cudaEvent_t) { return cudaSuccess; }
+inline cudaError_t cudaEventElapsedTime(float *ms, cudaEvent_t, cudaEvent_t) { *ms = 0.f; return cudaSuccess; }
 inline cudaError_t cudaMemcpyAsync(void *dst, const void *src, size_t bytes, int, cudaStream_t) { std::memcpy(dst, src, bytes); return cudaSuccess; }
 inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
 inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t *s, int) { *s = nullptr; return cudaSuccess; }

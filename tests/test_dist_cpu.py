@@ -129,3 +129,20 @@ def test_block_cache_never_frees_on_a_rank_thread():
     subprocess.run(["make", "-C", os.path.dirname(exe), "block_cache_check"], check=True, stdout=subprocess.DEVNULL)
     r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout
+
+
+def test_multi_gpu_layer_source_on_the_host_with_a_blocking_nccl_stand_in():
+    """csrc/rtb_dist.cu itself (rtb_render_multi: a thread per device) compiled for the host, 8 rank threads against a stand-in
+    for NCCL that blocks as NCCL does: tile and sample frames complete on rank 0; a rank that fails returns an error instead of
+    leaving the others in the collective; no rank thread calls cudaFree however full the block cache is (the 8-GPU hang of r02l);
+    and, as the negative control, with the deferral switched off rank threads DO free"""
+    import os
+    import subprocess
+    import _util
+    d = os.path.join(_util.ROOT, "tests", "devsim")
+    subprocess.run(["make", "-C", d, "dist_emul_check"], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    exe, lib = os.path.join(d, "dist_emul_check"), os.path.join(d, "libfakenccl.so")
+    r = subprocess.run([exe, lib], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok") and "FAILED" not in r.stdout, r.stdout
+    r = subprocess.run([exe, lib], capture_output=True, text=True, timeout=300, env=dict(os.environ, DIST_EMUL_NO_DEFER="1"))
+    assert r.returncode != 0 and "FAILED  no cudaFree on a thread that holds a rank" in r.stdout, r.stdout
