@@ -397,16 +397,21 @@ struct Builder {
 #pragma omp critical
             todo.insert(todo.end(), mine.begin(), mine.end());
         }
-        // large ranges first (they spawn tasks of their own), the many small ones dealt out dynamically
+        // Large ranges first (they spawn tasks of their own); then a fixed number of tasks, each taking every T-th range of the
+        // size-ordered list.  (A taskloop with a grain size made 1400 tasks for 22 k ranges, and libgomp runs a taskloop of more
+        // than 64 x threads tasks serially on the encountering thread: the ranges the GPU builder handed over at 64 - 256
+        // triangles were built by ONE thread -- 1.7 s at 10 M triangles where 4096 took 0.6 s.)
         std::sort(todo.begin(), todo.end(), [&](uint32_t x, uint32_t y) { return top[x].count != top[y].count ? top[x].count > top[y].count : x < y; });
 #pragma omp parallel
 #pragma omp single
         {
-#pragma omp taskloop default(shared) grainsize(16)
-            for (size_t i = 0; i < todo.size(); ++i) {
-                const GpuTopNode &g = top[todo[i]];
-                build(todo[i], g.first, g.count, nullptr);
-            }
+            const size_t T = std::min<size_t>(todo.size(), (size_t) omp_get_num_threads() * 16);
+#pragma omp taskloop default(shared) num_tasks(T)
+            for (size_t k = 0; k < T; ++k)
+                for (size_t i = k; i < todo.size(); i += T) {
+                    const GpuTopNode &g = top[todo[i]];
+                    build(todo[i], g.first, g.count, nullptr);
+                }
         }
         for (size_t t = nt; t-- > 0;) {
             TNode &nd = pool[t];
@@ -425,9 +430,11 @@ void HostTriangles::permute(const std::vector<uint32_t> &order) {
         if (vec.empty()) return;   // (an attribute array that has not been assembled)
         T out;
         resize_huge(out, n * stride);
-#pragma omp taskloop default(shared) grainsize(65536)
-        for (size_t i = 0; i < n; ++i)
-            std::memcpy(&out[i * stride], &vec[(size_t) order[i] * stride], stride * sizeof(out[0]));
+        const size_t parts = std::max<size_t>(1, std::min<size_t>((n + 65535) / 65536, (size_t) omp_get_num_threads() * 32));   // (libgomp serialises a taskloop of > 64 x threads tasks)
+#pragma omp taskloop default(shared) num_tasks(parts)
+        for (size_t c = 0; c < parts; ++c)
+            for (size_t i = chunk_at(n, parts, c), e = chunk_at(n, parts, c + 1); i < e; ++i)
+                std::memcpy(&out[i * stride], &vec[(size_t) order[i] * stride], stride * sizeof(out[0]));
         vec.swap(out);
     };
     apply(pos, 9);
