@@ -269,6 +269,37 @@ int rtb_closest_hit_device(rtb_scene *scene, const float *d_rays6, size_t n, int
                            int32_t *d_id, float *d_t, float *d_u, float *d_v, uint8_t *d_inside,
                            unsigned long long *d_counters, void *stream);
 
+/* rtb_closest_hit_device for callers that are not allowed to allocate device memory.  (No counterpart in the reference:
+ * its BVH::intersect runs on the host and has no such concern.)
+ *
+ * Who this is for.  Every other compute entry point may reach cudaMalloc / cudaFree behind the scenes: scenes keep
+ * cudaMalloc'ed cursors, staging and path-state blocks grow on demand and go through the block cache.  Some callers cannot
+ * have that happen on their thread:
+ *   - a rank thread that shares the process with an NCCL collective in flight: cudaMalloc / cudaFree wait for the whole
+ *     device, the collective waits for this rank -- the 8-GPU hang recorded in DESIGN.md section 7 was exactly this;
+ *   - a plugin inside a host that has handed all device memory to its own pool (a caching allocator, a renderer's arena):
+ *     the driver has nothing left to give, or the host forbids calls that synchronise the device;
+ *   - a frame loop with a latency budget, where an implicit device-wide synchronisation stalls every other stream.
+ * This call allocates nothing, frees nothing and calls no library routine that does.  The scene, the rays and the outputs
+ * are the caller's, as for rtb_closest_hit_device (same arguments, same results bit for bit, asynchronous on `stream`).
+ * The one piece of working memory the queue kernel needs -- the cursor its warps advance to claim rays -- lives in a
+ * 16 KB table compiled into librtb.so (64 cursors, one per 256-byte line, used in turn).  Consequences:
+ *   - every GPU on which the library's kernels are loaded holds those 16 KB until the process exits;
+ *   - a cursor is 32 bits wide: at most RTB_CLOSEST_HIT_STATIC_MAX_RAYS rays per call, more is refused with
+ *     RTB_ERR_INVALID (the other entry point switches kernels instead; this one asks the caller to split the batch);
+ *   - the table is shared by all scenes and threads of the process on that GPU and keeps what the last call left in it.
+ *     The call clears its cursor itself (a memset ordered on `stream` in front of the kernel), so no call depends on
+ *     earlier contents -- but calls that overlap on the GPU (different streams or threads, 64 or more in flight) can be
+ *     handed the same cursor and then race; keep such calls ordered;
+ *   - the first call on a device looks up where the table lives on that device (cudaGetSymbolAddress, once per device,
+ *     with that device current).  Make that first call ahead of time -- n == 0 is enough -- and outside any stream
+ *     capture.
+ * RTB_CULL_REFERENCE is accepted too; its kernel keeps no cursor and touches the table not at all.                    */
+#define RTB_CLOSEST_HIT_STATIC_MAX_RAYS 0xFFFFFEFFu
+int rtb_closest_hit_static(rtb_scene *scene, const float *d_rays6, size_t n, int cull_mode,
+                           int32_t *d_id, float *d_t, float *d_u, float *d_v, uint8_t *d_inside,
+                           unsigned long long *d_counters, void *stream);
+
 /* Measurement aid (no reference counterpart): L2 bandwidth of `device` on a `bytes`-sized buffer (choose one that fits the
  * L2) -- coalesced streaming reads, and 64-byte records gathered at random indices (an incoherent ray's node / triangle
  * fetch without the arithmetic).  bench.py reports the traversal's algorithmic bytes against both.                    */

@@ -19,6 +19,7 @@ RTB_OK, RTB_ERR_INVALID, RTB_ERR_NO_DEVICE, RTB_ERR_CUDA, RTB_ERR_IO = 0, 1, 2, 
 CULL_REFERENCE, CULL_GLOBAL = 0, 1
 RENDER_COUNTERS, RENDER_REFERENCE_CULL, RENDER_MEGAKERNEL, RENDER_STAGE_TIMES = 1, 2, 4, 8
 REQUEST_COUNTERS = 0xFFFFFFFFFFFFFFFF
+CLOSEST_HIT_STATIC_MAX_RAYS = 0xFFFFFEFF
 
 # every symbol include/rtb.h declares (tests/test_abi.py checks the library exports all of them)
 ABI_SYMBOLS = [
@@ -27,7 +28,7 @@ ABI_SYMBOLS = [
     "rtb_host_scene_build_seconds", "rtb_host_scene_build_info", "rtb_build_bvh", "rtb_host_scene_destroy",
     "rtb_host_scene_raw_geometry", "rtb_scene_create_raw", "rtb_scene_read_buffer",
     "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_device", "rtb_scene_traversal_bytes", "rtb_scene_upload_bytes", "rtb_scene_launches", "rtb_scene_stage_ms",
-    "rtb_closest_hit", "rtb_closest_hit_device", "rtb_light_pdf", "rtb_measure_l2",
+    "rtb_closest_hit", "rtb_closest_hit_device", "rtb_closest_hit_static", "rtb_light_pdf", "rtb_measure_l2",
     "rtb_render", "rtb_render_device", "rtb_resolve_device", "rtb_render_local_rows", "rtb_render_global_row",
     "rtb_render_resume", "rtb_render_resume_device", "rtb_render_state_bytes", "rtb_scene_set_progress",
     "rtb_release_cached_memory",
@@ -138,6 +139,7 @@ def lib():
         L.rtb_scene_device.argtypes = [C.c_void_p]
         L.rtb_closest_hit.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int] + [C.c_void_p] * 5 + [C.POINTER(Stats)]
         L.rtb_closest_hit_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int] + [C.c_void_p] * 7
+        L.rtb_closest_hit_static.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int] + [C.c_void_p] * 7
         L.rtb_light_pdf.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.rtb_measure_l2.argtypes = [C.c_int, C.c_size_t, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.rtb_render.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.POINTER(Stats)]
@@ -400,6 +402,12 @@ class Scene:
 
     def closest_hit_device(self, d_rays, n, cull, d_id, d_t=None, d_u=None, d_v=None, d_inside=None, d_counters=None, stream=0):
         _check(lib().rtb_closest_hit_device(self.h, _ptr(d_rays), n, cull, _ptr(d_id), _ptr(d_t), _ptr(d_u), _ptr(d_v),
+                                            _ptr(d_inside), _ptr(d_counters), C.c_void_p(stream)))
+
+    def closest_hit_static(self, d_rays, n, cull, d_id, d_t=None, d_u=None, d_v=None, d_inside=None, d_counters=None, stream=0):
+        """rtb_closest_hit_static: closest_hit_device for callers that must not allocate -- the ray cursor comes from a
+        table inside librtb.so; at most CLOSEST_HIT_STATIC_MAX_RAYS rays per call (include/rtb.h)."""
+        _check(lib().rtb_closest_hit_static(self.h, _ptr(d_rays), n, cull, _ptr(d_id), _ptr(d_t), _ptr(d_u), _ptr(d_v),
                                             _ptr(d_inside), _ptr(d_counters), C.c_void_p(stream)))
 
     def light_pdf(self, rays):

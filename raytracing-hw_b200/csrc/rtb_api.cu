@@ -571,6 +571,27 @@ int rtb_closest_hit_device(rtb_scene *scene, const float *d_rays6, size_t n, int
     return RTB_OK;
 }
 
+// rtb_closest_hit_device for a caller that must not allocate device memory (include/rtb.h): the queue cursor comes from a
+// table compiled into the library (csrc/rtb_kernels.cu), nothing on this path calls cudaMalloc / cudaFree.
+int rtb_closest_hit_static(rtb_scene *scene, const float *d_rays6, size_t n, int cull_mode, int32_t *d_id, float *d_t, float *d_u,
+                           float *d_v, uint8_t *d_inside, unsigned long long *d_counters, void *stream) {
+    if (!scene || (n > 0 && (!d_rays6 || !d_id))) { rtb::set_error("rtb_closest_hit_static: null argument"); return RTB_ERR_INVALID; }
+    if (cull_mode != RTB_CULL_REFERENCE && cull_mode != RTB_CULL_GLOBAL) { rtb::set_error("rtb_closest_hit_static: bad cull mode"); return RTB_ERR_INVALID; }
+    if (n > (size_t) RTB_CLOSEST_HIT_STATIC_MAX_RAYS) {
+        rtb::set_error("rtb_closest_hit_static: " + std::to_string(n) + " rays in one call; the built-in 32-bit ray cursor serves at most " +
+                       std::to_string((unsigned long long) RTB_CLOSEST_HIT_STATIC_MAX_RAYS) + " (split the batch)");
+        return RTB_ERR_INVALID;
+    }
+    RTB_CUDA(cudaSetDevice(scene->device));
+    const cudaError_t e = rtb::launch_closest_hit_static(scene->d, scene->device, d_rays6, n, cull_mode, d_id, d_t, d_u, d_v, d_inside,
+                                                         d_counters, (cudaStream_t) stream);
+    if (e != cudaSuccess) {
+        rtb::set_error(std::string("rtb_closest_hit_static: ") + cudaGetErrorString(e));
+        return RTB_ERR_CUDA;
+    }
+    return RTB_OK;
+}
+
 // Host-pointer variant: the batch is cut into chunks that flow through three streams so that the host->device copy of
 // chunk k+1 and the device->host copy of chunk k-1 overlap the traversal of chunk k.
 int rtb_closest_hit(rtb_scene *scene, const float *rays6, size_t n, int cull_mode, int32_t *id, float *t, float *u, float *v,

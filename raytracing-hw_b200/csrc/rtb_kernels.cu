@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 #include "rtb_shade.cuh"
 #include "rtb_trace.cuh"
 
@@ -173,6 +174,43 @@ void launch_closest_hit(const DScene &sc, const float *d_rays6, size_t n, int cu
         if (count) k_closest_hit<1, true><<<grid, block, 0, stream>>>(sc, d_rays6, n, d_id, d_t, d_u, d_v, d_inside, d_counters);
         else k_closest_hit<1, false><<<grid, block, 0, stream>>>(sc, d_rays6, n, d_id, d_t, d_u, d_v, d_inside, d_counters);
     }
+}
+
+// ---- closest hit for callers that must not allocate (rtb_closest_hit_static, include/rtb.h) --------------------------
+// The persistent queue kernel needs one word of global memory besides its inputs and outputs: the cursor its warps
+// advance to claim rays.  A scene owns cudaMalloc'ed cursors; this variant takes the cursor from a table that is part
+// of the library image instead, so the call path contains no allocation at all.  64 cursors, one per 256-byte line
+// (16 KB on every GPU that loads librtb.so, until the process exits), handed out round-robin per device; a cursor is
+// cleared by a stream-ordered memset in front of the launch that uses it, because the table keeps whatever the last
+// call left in it.
+constexpr unsigned kStaticCursors = 64;
+constexpr unsigned kStaticCursorStride = 256 / sizeof(unsigned);
+constexpr int kStaticMaxDevices = 64;
+static __device__ __align__(256) unsigned g_static_cursors[kStaticCursors * kStaticCursorStride];
+
+// `device` must be the current device.  In host code `g_static_cursors` is only a handle for the runtime, not an address
+// a kernel could use: the table's address on THIS device is asked for once (cudaGetSymbolAddress) and remembered.
+cudaError_t launch_closest_hit_static(const DScene &sc, int device, const float *d_rays6, size_t n, int cull_mode, int *d_id, float *d_t,
+                                      float *d_u, float *d_v, uint8_t *d_inside, unsigned long long *d_counters, cudaStream_t stream) {
+    static std::mutex mu;
+    static unsigned *table[kStaticMaxDevices] = {};
+    static unsigned next[kStaticMaxDevices] = {};
+    if (device < 0 || device >= kStaticMaxDevices) return cudaErrorInvalidDevice;
+    unsigned *cursor = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!table[device]) {
+            void *p = nullptr;
+            const cudaError_t e = cudaGetSymbolAddress(&p, g_static_cursors);
+            if (e != cudaSuccess) return e;
+            table[device] = static_cast<unsigned *>(p);
+        }
+        cursor = table[device] + (size_t) (next[device]++ % kStaticCursors) * kStaticCursorStride;
+    }
+    // (launch_closest_hit clears the cursor on `stream` before the queue kernel; RTB_CULL_REFERENCE runs the
+    // one-ray-per-thread kernel, which has no cursor)
+    launch_closest_hit(sc, d_rays6, n, cull_mode, d_id, d_t, d_u, d_v, d_inside, d_counters, cursor, stream);
+    return cudaGetLastError();
 }
 
 // ManyLightsDistribution::pdf (src/utils/random.cpp:179-188) for a batch of (point, direction).

@@ -7,6 +7,10 @@ namespace rtb {
 
 void launch_closest_hit(const DScene &sc, const float *d_rays6, size_t n, int cull_mode, int *d_id, float *d_t, float *d_u,
                         float *d_v, uint8_t *d_inside, unsigned long long *d_counters, unsigned *d_queue_head, cudaStream_t stream);
+// the same launch with the ray-queue cursor taken from a table inside the library image (no allocation anywhere on the
+// path); `device` = the current device.  rtb_kernels.cu
+cudaError_t launch_closest_hit_static(const DScene &sc, int device, const float *d_rays6, size_t n, int cull_mode, int *d_id, float *d_t,
+                                      float *d_u, float *d_v, uint8_t *d_inside, unsigned long long *d_counters, cudaStream_t stream);
 int persistent_grid(int threads_per_block, int blocks_per_sm);
 constexpr int kDefaultTraceMode = 4;       // rtb_trace.cuh: 3 / 4 / 5 = one / two / three steps per refill vote (RTB_TRACE_MODE)
 int trace_mode();
