@@ -49,11 +49,14 @@ struct BlockCache {
         }
         *got = bytes;
         cudaError_t e = cudaMalloc(out, bytes);
-        if (e != cudaSuccess) {   // out of memory with blocks parked here: give them back and try once more
+        if (e != cudaSuccess && !defer_flag()) {   // out of memory with blocks parked here: give them back and try once more
             cudaGetLastError();
             trim(device);
             e = cudaMalloc(out, bytes);
         }
+        // (a thread that defers its frees -- a rank thread of rtb_render_multi -- must not trim either: trim is cudaFree.  It
+        // gets the error; rtb_render_multi hands the cache back once its threads have joined, so the caller's next frame finds
+        // the memory)
         return e;
     }
     // Frees are DEFERRED on threads that asked for it (defer_frees): a thread that renders one device of a multi-device frame

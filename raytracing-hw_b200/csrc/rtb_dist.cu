@@ -364,7 +364,13 @@ int rtb_render_multi(rtb_scene *const *scenes, int n, const rtb_render_params *f
         else for (auto *c : fresh) rtb_comm_destroy(c);
     }
     for (int r = 0; r < n; ++r)
-        if (rcs[(size_t) r] != RTB_OK) { rtb::set_error("rank " + std::to_string(r) + ": " + errs[(size_t) r]); return rcs[(size_t) r]; }
+        if (rcs[(size_t) r] != RTB_OK) {
+            // a rank thread that ran out of memory could not trim the block cache itself (BlockCache::acquire): do it here, where
+            // no thread holds a rank, so that calling again has the cached blocks' memory to work with
+            rtb_release_cached_memory();
+            rtb::set_error("rank " + std::to_string(r) + ": " + errs[(size_t) r]);
+            return rcs[(size_t) r];
+        }
     if (stats)
         for (int r = 0; r < n; ++r) {
             stats->closest_hit_rays += st[(size_t) r].closest_hit_rays;

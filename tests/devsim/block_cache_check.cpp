@@ -55,6 +55,28 @@ int main() {
     c.flush_deferred();
     expect(c.deferred.empty() && frees_total() > before, "flush_deferred frees them");
     expect(c.total <= c.limit(), "the byte limit holds");
+    // out of memory: a plain thread gives the cached blocks of the device back and tries again; a deferring thread does
+    // neither (trim is cudaFree) and reports the error -- rtb_render_multi trims after its threads have joined
+    c.acquire(0, 3000000, &p, &got);
+    c.release(0, p, got);   // something parked on device 0
+    {
+        const int f0 = frees_total();
+        emu_malloc_fail_next = 1;
+        expect(c.acquire(0, 20000000, &q, &got) == cudaSuccess && frees_total() > f0, "out of memory: the cache is trimmed and the request retried");
+        c.release(0, q, got);
+        const int f1 = frees_total();
+        cudaError_t e_thread = cudaSuccess;
+        std::thread t2([&] {
+            rtb::BlockCache::defer_flag() = true;
+            void *a = nullptr;
+            size_t g = 0;
+            emu_malloc_fail_next = 1;
+            e_thread = c.acquire(0, 50000000, &a, &g);
+        });
+        t2.join();
+        emu_malloc_fail_next = 0;
+        expect(e_thread != cudaSuccess && frees_total() == f1, "out of memory on a deferring thread: an error, no cudaFree");
+    }
     // an oversized block is never kept
     c.acquire(0, (size_t) 80 << 20, &p, &got);
     const int f0 = frees_total();

@@ -56,6 +56,7 @@ void launch_resolve(const float *accum, size_t n_pixels, int, uint8_t *rgb8, cud
 extern "C" {
 const char *rtb_last_error(void) { return t_error.c_str(); }
 int rtb_device_count(void) { return 8; }
+void rtb_release_cached_memory(void) { g_blocks.flush_deferred(); g_blocks.trim(-1); }   // as csrc/rtb_api.cu
 int rtb_scene_device(const rtb_scene *s) { return s->device; }
 unsigned long long rtb_scene_launches(const rtb_scene *s) { return s->launches; }
 int rtb_render_local_rows(const rtb_render_params *p) {   // as csrc/rtb_api.cu
@@ -107,12 +108,15 @@ int main(int argc, char **argv) {
     std::vector<rtb_scene *> ptr;
     for (int d = 0; d < N; ++d) { sc[(size_t) d].device = d; ptr.push_back(&sc[(size_t) d]); }
     // a cache that is full of OTHER devices' blocks: every release from here on has to drop something
-    for (int i = 0; i < 40; ++i) {
-        void *p = nullptr;
-        size_t got = 0;
-        g_blocks.acquire(i % N, (size_t) (6 + i) << 20, &p, &got);   // (growing sizes: none is handed out again)
-        g_blocks.release(i % N, p, got);
-    }
+    auto fill_cache = [&] {
+        for (int i = 0; i < 40; ++i) {
+            void *p = nullptr;
+            size_t got = 0;
+            g_blocks.acquire(i % N, (size_t) (6 + i) << 20, &p, &got);   // (growing sizes: none is handed out again)
+            g_blocks.release(i % N, p, got);
+        }
+    };
+    fill_cache();
     int freed_before = 0;
     for (int v : emu_frees) freed_before += v;
     rtb_render_params f;
@@ -143,6 +147,7 @@ int main(int argc, char **argv) {
     expect(rc != RTB_OK, "the same in the sample split");
     alarm(60);
     sc[3].fail = 0;
+    fill_cache();   // (a failed frame hands the cache back to the driver -- on the calling thread: fill it again)
     f.substreams = 0;
     std::fill(img.begin(), img.end(), 0);
     rc = rtb_render_multi(ptr.data(), N, &f, RTB_SPLIT_TILE, img.data(), &st);

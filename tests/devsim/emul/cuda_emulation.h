@@ -30,7 +30,17 @@ inline cudaError_t cudaGetDevice(int *d) { *d = emu_device; return cudaSuccess; 
 inline cudaError_t cudaSetDevice(int d) { emu_device = d; return cudaSuccess; }
 inline cudaError_t cudaGetLastError() { return cudaSuccess; }
 inline const char *cudaGetErrorString(cudaError_t) { return "emulated"; }
-inline cudaError_t cudaMalloc(void **p, size_t bytes) { *p = std::malloc(bytes); return *p ? cudaSuccess : 2; }
+inline size_t emu_malloc_limit = ~(size_t) 0;   // tests: requests above this many bytes fail while emu_live_bytes-free accounting is off
+inline int emu_malloc_fail_next = 0;            // tests: the next k cudaMalloc calls report out of memory
+inline cudaError_t cudaMalloc(void **p, size_t bytes) {
+    if (bytes > emu_malloc_limit || emu_malloc_fail_next > 0) {
+        if (emu_malloc_fail_next > 0) --emu_malloc_fail_next;
+        *p = nullptr;
+        return 2;
+    }
+    *p = std::malloc(bytes);
+    return *p ? cudaSuccess : 2;
+}
 inline cudaError_t cudaFree(void *p) {
     if (p) {
         __sync_fetch_and_add(&emu_frees[emu_device & 63], 1);
