@@ -94,6 +94,9 @@ struct Decoder {
     int get_bits(int n) {
         if (n == 0) return 0;
         if (code_bits < n) grow();
+        // a marker inside the entropy data stops grow() early: out of bits on a truncated / corrupt file.  Answer zeros
+        // and leave the counter alone (it would go negative and the next grow() would shift by 32 or more)
+        if (code_bits < n) return 0;
         const unsigned v = code_buffer >> (32 - n);
         code_buffer <<= n;
         code_bits -= n;
@@ -336,7 +339,8 @@ bool parse_and_decode(Decoder &z) {
             z.n_comp = z.get8();
             if (prec != 8) { z.err = "JPEG: only 8-bit samples"; return false; }
             if (z.width <= 0 || z.height <= 0) { z.err = "JPEG with zero size"; return false; }
-            if ((size_t) z.width > 32768 || (size_t) z.height > 32768) { z.err = "JPEG too large"; return false; }
+            // (a header of a few hundred bytes must not be able to ask for gigabytes of planes: 2^28 pixels at most)
+            if ((size_t) z.width > 32768 || (size_t) z.height > 32768 || (size_t) z.width * (size_t) z.height > ((size_t) 1 << 28)) { z.err = "JPEG too large"; return false; }
             if (z.n_comp != 1 && z.n_comp != 3) { z.err = "JPEG: 1 or 3 components only"; return false; }
             if (L != 8 + 3 * z.n_comp) { z.err = "bad SOF length"; return false; }
             static const char rgb[3] = {'R', 'G', 'B'};

@@ -192,6 +192,30 @@ def test_bad_images_are_errors(tmp_path):
         rtb.HostScene.load_gltf(_image_gltf(str(tmp_path), ["x.jpg"]), 16, 16, 1)
 
 
+def test_oversized_and_truncated_jpegs(tmp_path):
+    """a header that announces 32768 x 32768 pixels is refused before anything is allocated; a file cut in the middle of
+    its entropy data (the EOI marker met while bits are still wanted) decodes to something or is refused -- it does not
+    run the bit reader's counter below zero (checked under -fsanitize in development; here: no crash, a full-size image)"""
+    jpg = os.path.join(str(tmp_path), "x.jpg")
+    sof0 = b"\xff\xc0\x00\x0b\x08\x80\x00\x80\x00\x01\x01\x11\x00"     # baseline, 8 bit, 32768 x 32768, one component
+    open(jpg, "wb").write(b"\xff\xd8" + sof0 + b"\xff\xd9")
+    with pytest.raises(Exception) as e:
+        rtb.HostScene.load_gltf(_image_gltf(str(tmp_path), ["x.jpg"]), 16, 16, 1)
+    assert "too large" in str(e.value)
+    PIL = pytest.importorskip("PIL.Image")
+    yy, xx = np.mgrid[0:64, 0:64]
+    img = np.stack([(xx * 3) % 256, (yy * 5) % 256, (xx + yy) % 256], -1).astype(np.uint8)
+    PIL.fromarray(img).save(jpg, quality=90, subsampling=2)
+    data = open(jpg, "rb").read()
+    for cut in (len(data) // 2, len(data) - 20, len(data) - 3):
+        open(jpg, "wb").write(data[:cut] + b"\xff\xd9")
+        try:
+            hs = rtb.HostScene.load_gltf(_image_gltf(str(tmp_path), ["x.jpg"]), 16, 16, 1)
+        except Exception:
+            continue
+        assert hs.textures()[0].shape == (64, 64, 4)
+
+
 def test_vertex_index_out_of_range_is_an_error(tmp_path):
     """a malformed file whose index accessor points past its vertex accessors is refused, not read out of bounds"""
     src = _util.scene_path("s7_4")
