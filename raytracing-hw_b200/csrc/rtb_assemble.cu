@@ -37,7 +37,9 @@ __global__ void __launch_bounds__(256) k_texture_quads(const uchar4 *texels, uin
 __global__ void __launch_bounds__(256) k_convert_level(const NodeItem *in, const unsigned *n_in_ptr, uint32_t n_nodes, uint32_t n_internal, uint32_t n_tris,
                                                        const float *aabb, const int32_t *links, BigLeafIndex big, DNode *nodes, NodeItem *out,
                                                        unsigned *n_out, int *error) {
-    const unsigned n_in = *n_in_ptr;
+    // (a frontier buffer holds n_internal items; after an overflow -- flagged in *error by the level before -- the counter
+    // is larger than that)
+    const unsigned n_in = min(*n_in_ptr, n_internal);
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_in; i += gridDim.x * blockDim.x) {
         NodeItem kids[2];
         int nk = 0;
@@ -104,9 +106,12 @@ int launch_convert_nodes(uint32_t n_nodes, uint32_t n_internal, uint32_t n_tris,
                                                  d_counts + (cur ^ 1), d_error);
         // the next frontier's size decides the next launch: one 4-byte read-back per level (a tree has ~log2(n) + a few levels)
         unsigned next = 0;
+        int flagged = 0;
         if (cudaMemcpyAsync(&next, d_counts + (cur ^ 1), sizeof(unsigned), cudaMemcpyDeviceToHost, stream) != cudaSuccess) return -1;
+        if (cudaMemcpyAsync(&flagged, d_error, sizeof(int), cudaMemcpyDeviceToHost, stream) != cudaSuccess) return -1;
         if (cudaMemsetAsync(d_counts + cur, 0, sizeof(unsigned), stream) != cudaSuccess) return -1;
         if (cudaStreamSynchronize(stream) != cudaSuccess) return -1;
+        if (flagged != 0) break;   // malformed input: the caller reads *d_error; no point in walking what is not a tree
         n_in = std::min(next, n_internal);
     }
     return levels;

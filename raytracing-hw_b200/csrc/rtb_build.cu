@@ -563,7 +563,9 @@ bool gpu_build_top(const float *tbox, const float *tcenter, size_t n_in, size_t 
     const size_t node_cap = (size_t) n / host_below + 2;
     d.nodes = A.take<LevelNode>(node_cap);
     d.next = A.take<LevelNode>(node_cap);
-    const size_t top_cap = std::min<size_t>(2 * (size_t) n + 1, 8 * ((size_t) n / host_below) + 1024);
+    // a legal tree of n triangles has at most 2 n - 1 nodes (the SAH may peel single triangles off): room for all of them
+    // (48 bytes each), so that an unbalanced scene does not throw the finished GPU build away
+    const size_t top_cap = 2 * (size_t) n + 1;
     d.top_cap = (uint32_t) top_cap;
     d.top = A.take<GpuTopNode>(top_cap);
     d.cnt = A.take<Counters>(1);

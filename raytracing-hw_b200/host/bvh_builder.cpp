@@ -525,6 +525,9 @@ void build_bvh(HostTriangles &tris, HostBvh &out, int threads) {
                 on_gpu = true;
             } else if (mode > 0 && std::getenv("RTB_BUILD_GPU_STRICT")) {
                 throw std::runtime_error("GPU BVH build failed: " + err);
+            } else if (err != "no CUDA device") {
+                // (same layout either way, but seconds slower on large scenes: say so once per build)
+                std::fprintf(stderr, "rtb: the GPU BVH build was discarded (%s); building on the host\n", err.c_str());
             }
         }
     }
