@@ -83,8 +83,10 @@ NcclApi *nccl() {
     return &api;
 }
 
+thread_local bool t_nccl_failed = false;   // an NCCL call failed on this thread (rtb_render_multi: the communicators are not kept)
 int nccl_fail(const char *what, int rc) {
     NcclApi *a = nccl();
+    t_nccl_failed = true;
     rtb::set_error(std::string(what) + ": " + (a->GetErrorString ? a->GetErrorString(rc) : "NCCL error"));
     return RTB_ERR_CUDA;
 }
@@ -254,13 +256,16 @@ int rtb_render_dist_device(rtb_scene *scene, rtb_comm *comm, const rtb_render_pa
         return rc;
     }
     RTB_NCCL(a->GroupStart());
+    int xfer = 0;   // first failure inside the group; the group is closed whatever happens (an open group swallows the thread's next NCCL calls)
     if (rank == 0) {
-        for (int r = 1; r < world; ++r)
-            if (rows[(size_t) r] > 0) RTB_NCCL(a->Recv((uint8_t *) side + m.row_off[r] * W * 3, (size_t) rows[(size_t) r] * W * 3, kNcclUint8, r, comm->comm, stream));
+        for (int r = 1; r < world && xfer == 0; ++r)
+            if (rows[(size_t) r] > 0) xfer = a->Recv((uint8_t *) side + m.row_off[r] * W * 3, (size_t) rows[(size_t) r] * W * 3, kNcclUint8, r, comm->comm, stream);
     } else if (local_rows > 0) {
-        RTB_NCCL(a->Send(local, (size_t) local_rows * W * 3, kNcclUint8, 0, comm->comm, stream));
+        xfer = a->Send(local, (size_t) local_rows * W * 3, kNcclUint8, 0, comm->comm, stream);
     }
-    RTB_NCCL(a->GroupEnd());
+    const int ended = a->GroupEnd();
+    if (xfer != 0) return nccl_fail(rank == 0 ? "ncclRecv" : "ncclSend", xfer);
+    if (ended != 0) return nccl_fail("ncclGroupEnd", ended);
     if (rank == 0 && d_rgb8_root) {
         const size_t total = W * 3 * H;
         k_place_rows<<<(unsigned) ((total + 255) / 256), 256, 0, stream>>>((const uint8_t *) side, d_rgb8_root, m);
@@ -323,6 +328,9 @@ int rtb_render_multi(rtb_scene *const *scenes, int n, const rtb_render_params *f
     std::vector<int> devs((size_t) n);
     for (int r = 0; r < n; ++r) devs[(size_t) r] = rtb_scene_device(scenes[r]);
     std::vector<rtb_comm *> *comms = nullptr;
+    for (int r = 0; r < n; ++r)
+        for (int q = 0; q < r; ++q)
+            if (devs[(size_t) r] == devs[(size_t) q]) { rtb::set_error("rtb_render_multi: two scenes on device " + std::to_string(devs[(size_t) r]) + " (one rank per device)"); return RTB_ERR_INVALID; }
     for (auto &k : kept) if (k.first == devs) comms = &k.second;
     std::vector<int> rcs((size_t) n, RTB_OK);
     std::vector<std::string> errs((size_t) n);
@@ -334,16 +342,30 @@ int rtb_render_multi(rtb_scene *const *scenes, int n, const rtb_render_params *f
         if (rc != RTB_OK) return rc;
         fresh.assign((size_t) n, nullptr);
     }
-    MultiSync sync;
+    MultiSync sync, presync;   // before the collective of the frame / before ncclCommInitRank (which waits for all n ranks)
     sync.n = n;
+    presync.n = n;
+    std::vector<char> nccl_bad((size_t) n, 0);
     std::vector<std::thread> th;
     for (int r = 0; r < n; ++r) {
         th.emplace_back([&, r] {
             rtb::blocks_defer_frees(true);   // no cudaFree on a thread that holds a rank (BlockCache::release)
             int e = RTB_OK;
             rtb_comm *c = comms ? (*comms)[(size_t) r] : nullptr;
+            t_nccl_failed = false;
             if (!comms) {
-                e = rtb_comm_create(id, n, r, devs[(size_t) r], &c);
+                // what can fail on ONE rank only is tried first and the ranks compare notes: a rank that cannot reach its device
+                // must not leave the other n - 1 waiting in ncclCommInitRank for ever
+                int pre = RTB_OK;
+                if (cudaSetDevice(devs[(size_t) r]) != cudaSuccess) {
+                    cudaGetLastError();
+                    rtb::set_error("rtb_render_multi: device " + std::to_string(devs[(size_t) r]) + " cannot be selected");
+                    pre = RTB_ERR_CUDA;
+                }
+                const int all = presync.arrive(r, pre);
+                if (pre == RTB_OK && all != RTB_OK) rtb::set_error("rtb_render_multi: another rank could not initialise");
+                e = pre != RTB_OK ? pre : all;
+                if (e == RTB_OK) e = rtb_comm_create(id, n, r, devs[(size_t) r], &c);
                 fresh[(size_t) r] = c;
             }
             // (a rank without a communicator cannot take part: it still has to be counted at the meeting point)
@@ -352,16 +374,28 @@ int rtb_render_multi(rtb_scene *const *scenes, int n, const rtb_render_params *f
             if (!sync.met[r]) sync.arrive(r, e);   // returned before the meeting point: the others must not wait
             if (c) c->sync = nullptr;
             if (e != RTB_OK) errs[(size_t) r] = rtb_last_error();
+            nccl_bad[(size_t) r] = t_nccl_failed ? 1 : 0;
             rcs[(size_t) r] = e;
         });
     }
     for (auto &t : th) t.join();
     rtb::blocks_flush_deferred();
+    bool nccl_failed = false;
+    for (char b : nccl_bad) nccl_failed = nccl_failed || b != 0;
     if (!comms) {
-        bool all = true;
+        bool all = !nccl_failed;
         for (auto *c : fresh) all = all && c != nullptr;
         if (all) kept.emplace_back(devs, fresh);
         else for (auto *c : fresh) rtb_comm_destroy(c);
+    } else if (nccl_failed) {
+        // a communicator that has reported an error is not used again: the next frame creates a new set
+        for (size_t k = 0; k < kept.size(); ++k)
+            if (&kept[k].second == comms) {
+                for (auto *c : kept[k].second) rtb_comm_destroy(c);
+                kept.erase(kept.begin() + (long) k);
+                break;
+            }
+        comms = nullptr;
     }
     for (int r = 0; r < n; ++r)
         if (rcs[(size_t) r] != RTB_OK) {

@@ -161,6 +161,23 @@ int main(int argc, char **argv) {
         rc = rtb_render_multi(ptr.data(), N, &f, k % 2 ? RTB_SPLIT_SAMPLE : RTB_SPLIT_TILE, img.data(), &st);
         if (rc != RTB_OK) bad = 1;
     }
+    // a NEW device list (communicators have to be created) with one device that cannot be selected: the other ranks must not
+    // be left in ncclCommInitRank, which waits for all of them (the alarm ends the test if they are)
+    {
+        alarm(60);
+        std::vector<rtb_scene *> rev(ptr.rbegin(), ptr.rend());
+        emu_bad_device = 5;
+        f.width = W; f.height = H; f.row_end = H; f.substreams = 0;
+        img.assign((size_t) W * H * 3, 0);
+        rc = rtb_render_multi(rev.data(), N, &f, RTB_SPLIT_TILE, img.data(), &st);
+        expect(rc != RTB_OK && std::string(rtb_last_error()).find("rank") != std::string::npos, "a rank without its device: an error before the communicators are created");
+        emu_bad_device = -1;
+        rc = rtb_render_multi(rev.data(), N, &f, RTB_SPLIT_TILE, img.data(), &st);
+        expect(rc == RTB_OK && rows_ok(), "the same device list renders once the device is back");
+        rtb_scene *twice[2] = {ptr[1], ptr[1]};
+        rc = rtb_render_multi(twice, 2, &f, RTB_SPLIT_TILE, img.data(), &st);
+        expect(rc == RTB_ERR_INVALID, "two ranks on one device are refused");
+    }
     alarm(0);
     expect(g_frees_on_rank_threads.load() == 0, "no cudaFree on a thread that holds a rank");
     int freed = 0;

@@ -27,7 +27,8 @@ inline thread_local int emu_device = 0;    // the current device is per thread, 
 inline int emu_frees[64] = {};             // cudaFree calls by current device
 inline void (*emu_free_hook)() = nullptr;  // called by every cudaFree of a non-null pointer (tests: who frees, and when)
 inline cudaError_t cudaGetDevice(int *d) { *d = emu_device; return cudaSuccess; }
-inline cudaError_t cudaSetDevice(int d) { emu_device = d; return cudaSuccess; }
+inline int emu_bad_device = -1;            // tests: cudaSetDevice(this device) fails
+inline cudaError_t cudaSetDevice(int d) { if (d == emu_bad_device) return 101; emu_device = d; return cudaSuccess; }
 inline cudaError_t cudaGetLastError() { return cudaSuccess; }
 inline const char *cudaGetErrorString(cudaError_t) { return "emulated"; }
 inline size_t emu_malloc_limit = ~(size_t) 0;   // tests: requests above this many bytes fail while emu_live_bytes-free accounting is off
