@@ -44,8 +44,12 @@ for stage in "$@"; do
                     echo "--- $v"
                     RTB_LIB=$v timeout 600 $PY bench.py --steps 3 --warmup 3 --spp $SPP --no-cpu-baseline --no-e2e 2>/dev/null | $PY -c 'import sys,json; d=json.loads(sys.stdin.read()); r=d["roofline"]; print(json.dumps({"value": d["value"], "trace_ms": r["kernel_ms_total"], "other_ms": r["other_kernels_ms_total"], "kernel_mrays_per_s": r["kernel_mrays_per_s"]}))'
                   done > $OUT/${TAG}_variants_spp$SPP.txt 2>&1; cat $OUT/${TAG}_variants_spp$SPP.txt ;;
-    multi)        timeout 900 $PY -m pytest tests/test_gpu_dist.py -m gpu -x -q > $OUT/${TAG}_tests_dist_n$NGPU.log 2>&1; tail -3 $OUT/${TAG}_tests_dist_n$NGPU.log
-                  trun $NGPU tools/check_multigpu.py --full > $OUT/${TAG}_check_multigpu_n$NGPU.log 2>&1; tail -2 $OUT/${TAG}_check_multigpu_n$NGPU.log ;;
+    multi)        timeout 600 $PY -m pytest tests/test_gpu_dist.py -m gpu -x -q > $OUT/${TAG}_tests_dist_n$NGPU.log 2>&1; tail -3 $OUT/${TAG}_tests_dist_n$NGPU.log
+                  timeout 600 $PY -m torch.distributed.run --nnodes=1 --nproc-per-node $NGPU --master-addr 127.0.0.1 --master-port $((29500 + RANDOM % 400)) tools/check_multigpu.py --full > $OUT/${TAG}_check_multigpu_n$NGPU.log 2>&1; tail -2 $OUT/${TAG}_check_multigpu_n$NGPU.log ;;
+    target)       # north_star's target sentence through the CLI (a thread per GPU), image checked against the one-GPU frame
+                  timeout 900 $PY tools/target_run.py --spp ${TARGET_SPP:-1024} --out $OUT/${TAG}_target_run_n$NGPU.json > /dev/null 2> $OUT/${TAG}_target_run_n$NGPU.err; cut -c1-600 $OUT/${TAG}_target_run_n$NGPU.json ;;
+    bench_auto)   # the driver's command at N GPUs: tile split headline + sample split secondary
+                  timeout 900 $PY -m torch.distributed.run --nnodes=1 --nproc-per-node $NGPU --master-addr 127.0.0.1 --master-port $((29500 + RANDOM % 400)) bench.py --gpus $NGPU --steps ${STEPS:-3} --warmup 3 > $OUT/${TAG}_bench_n${NGPU}_auto.json 2> $OUT/${TAG}_bench_n${NGPU}_auto.err; cut -c1-300 $OUT/${TAG}_bench_n${NGPU}_auto.json ;;
     scale)        for split in sample tile; do
                     trun $NGPU bench.py --gpus $NGPU --steps ${STEPS:-3} --warmup 3 --split $split > $OUT/${TAG}_bench_n${NGPU}_$split.json 2> $OUT/${TAG}_bench_n${NGPU}_$split.err; cut -c1-300 $OUT/${TAG}_bench_n${NGPU}_$split.json
                   done ;;
