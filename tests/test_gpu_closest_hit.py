@@ -143,12 +143,18 @@ def test_full_size_properties():
     assert np.array_equal(first[1], want["id"]) and np.array_equal(first[2], want["t"])
 
 
+# RTB_CULL_GLOBAL against the reference's recursion on rays aimed at shared vertices / edges: {scene: (rays whose id differs,
+# of 200 000; largest relative gap of t -- ours is the smaller one)}.  Not exact ties: near-ties.
+NEAR_TIES = {"s7_1": (205, 1.4e-5), "s7_4": (904, 5.6e-5), "s6_1": (212, 5.3e-6), "soup_10k": (0, 0.0), "sponza_small": (471, 3.4e-4)}
+
+
 @pytest.mark.parametrize("name", SCENES)
 def test_decision_boundary_rays(name, host_scene):
     """rays ON the box test's decision boundaries (zero direction components, origins on box planes, rays through box
     corners; tests/_util.py: edge_rays): the queue kernel (form 3: box_test_z, one pop / decode site, 256-bit loads)
     against the in-order global-best traversal of the same arithmetic -- every bit -- and against the reference's
-    recursion (twin): same hit / miss, equal t,u,v where the ids agree, the rest are the documented tie case"""
+    recursion (twin): same hit / miss, equal t,u,v where the ids agree, the rest are the documented near-tie deviation
+    (NEAR_TIES: measured count and gap per scene)"""
     g = _util.load_golden(name)
     hs = host_scene(name)
     rays = _util.edge_rays(hs, g["root_box"], 200_000, seed=79)
@@ -163,8 +169,12 @@ def test_decision_boundary_rays(name, host_scene):
     for k in ("t", "u", "v", "inside"):
         assert np.array_equal(got[k][hit & same], want[k][hit & same]), k
     tie = hit & ~same
-    assert np.count_nonzero(tie) <= 0.005 * rays.shape[0]
+    # measured on these seeded batches (200 000 rays each; the CPU mirror of the kernel gives the same numbers): a regression
+    # in the culling bound shows as a larger count or a wider gap
+    assert np.count_nonzero(tie) <= NEAR_TIES[name][0], (name, np.count_nonzero(tie))
     assert np.all(got["t"][tie] <= want["t"][tie])
+    if tie.any():
+        assert float(np.max((want["t"][tie] - got["t"][tie]) / want["t"][tie])) <= NEAR_TIES[name][1]
     ref = rtb.Scene(hs, 0).closest_hit(rays, cull=rtb.CULL_REFERENCE)
     for k in ("id", "t", "u", "v", "inside"):
         assert np.array_equal(ref[k], want[k]), k
